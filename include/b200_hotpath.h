@@ -1,0 +1,106 @@
+/*
+ * b200_hotpath.h — C-ABI of the B200-native (sm_100a) serving hot path.
+ *
+ * Every entry point takes raw DEVICE pointers, sizes/strides and a CUDA stream
+ * (cudaStream_t passed as void*), returns an int status (0 = ok, non-zero =
+ * error; text via b200_last_error()) and launches asynchronously on the given
+ * stream.  No torch types cross this boundary.  The Python host side
+ * (sglang_security_b200/*.py) binds it with ctypes and raises on non-zero
+ * status, mirroring the reference convention that kernels raise
+ * (TORCH_CHECK -> RuntimeError, e.g. sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1078-1108).
+ *
+ * Each function cites the reference interface (file:line under the reference
+ * tree) it replaces.  Strides are in ELEMENTS of the tensor's dtype unless the
+ * name says bytes.
+ */
+#ifndef B200_HOTPATH_H_
+#define B200_HOTPATH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* dtype codes used by the *_dtype arguments */
+enum b200_dtype {
+  B200_BF16 = 0,
+  B200_F16 = 1,
+  B200_F32 = 2,
+  B200_FP8_E4M3 = 3
+};
+
+/* ---- library ---------------------------------------------------------- */
+int b200_version(void);
+/* Thread-local text of the last error raised by a b200_* call in this thread. */
+const char* b200_last_error(void);
+/* Number of kernels this library has launched so far in this process
+ * (bench.py's gpu_launches counter). */
+int64_t b200_launch_count(void);
+
+/* Per-kernel device timing for bench.py's roofline leg: while enabled, the dominant kernels are
+ * bracketed by CUDA events on the launching stream (not during graph capture).
+ * b200_timing_read sums and clears the records of kernel `name` (NULL/"" = all). Names:
+ * "attn_decode_split", "attn_merge", "kv_write", "attn_extend", "fp8_gemm", "w4a16_gemm", ... */
+int b200_timing_enable(int on);
+int b200_timing_read(const char* name, int64_t* launches, double* total_ms);
+
+/* ---- KV pool write ---------------------------------------------------- */
+/* Replaces MHATokenToKVPool.set_kv_buffer (python/sglang/srt/mem_cache/memory_pool.py:378-412):
+ *   k_cache[loc[t], :, :] = k[t, :, :]; v_cache[loc[t], :, :] = v[t, :, :]   (bit-exact byte copy)
+ * k, v          [num_tokens, Hkv, D] rows of row_bytes contiguous bytes, token stride given in bytes
+ *               (k/v are strided slices of the fused qkv output, models/llama.py:186-189)
+ * k_cache/v_cache  [size+page, Hkv, D] contiguous rows of row_bytes
+ * loc           int64 [num_tokens] slot ids (out_cache_loc)                       */
+int b200_kv_write(const void* k, const void* v, int64_t k_token_stride_bytes,
+                  int64_t v_token_stride_bytes, void* k_cache, void* v_cache,
+                  const int64_t* loc, int num_tokens, int k_row_bytes, int v_row_bytes,
+                  void* stream);
+
+/* ---- request -> token index gather ------------------------------------ */
+/* Replaces create_flashinfer_kv_indices_triton (python/sglang/srt/layers/attention/utils.py:5-41):
+ *   kv_indices[kv_indptr[b] + i] = req_to_token[req_pool_indices[b], kv_start[b] + i], i < lens[b]
+ * req_pool_indices / lens are int64 (ForwardBatch fields) ; kv_start may be NULL.   */
+int b200_kv_indices(const int32_t* req_to_token, int64_t req_to_token_stride,
+                    const int64_t* req_pool_indices, const int64_t* lens,
+                    const int32_t* kv_indptr, const int32_t* kv_start, int32_t* kv_indices,
+                    int bs, void* stream);
+
+/* ---- paged decode attention ------------------------------------------- */
+/* Replaces AttentionBackend.forward_decode's kernel (torch_native_backend.py:112-180 as the
+ * numerical oracle; triton_ops/decode_attention.py:682-733 as the GPU implementation):
+ * for every request b and query head h
+ *   o[b,h,:] = softmax_t( scale * q[b,h,:] . K[slot(b,t), h/g, :] ) @ V[slot(b,t), h/g, :],
+ *   slot(b,t) = req_to_token[req_pool_indices[b], t],  t < seq_lens[b]
+ * Split-KV: num_splits partial results go to `workspace`, merged by a second kernel.
+ * q   [bs, Hq, D]   token stride q_stride elements; head stride D
+ * o   [bs, Hq, Dv]  token stride o_stride elements
+ * k_cache/v_cache [slots, Hkv, D] row stride kv_row_stride elements (normally Hkv*D)
+ * dtype: B200_BF16 or B200_F16 for q/k/v/o.  logit_cap <= 0 disables tanh capping.
+ * workspace must hold b200_attn_decode_workspace_bytes(bs, Hq, Dv, num_splits) bytes. */
+size_t b200_attn_decode_workspace_bytes(int bs, int Hq, int Dv, int num_splits);
+/* Split-count heuristic (replaces get_num_kv_splits_triton, triton_backend.py:23-72, with a
+ * host-side choice that needs no device sync): avg_len = expected tokens per request.       */
+int b200_attn_decode_num_splits(int bs, int Hkv, int group, int D, int64_t avg_len, int num_sms);
+int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                     int64_t kv_row_stride, void* o, int64_t o_stride,
+                     const int32_t* req_to_token, int64_t req_to_token_stride,
+                     const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
+                     int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                     void* workspace, size_t workspace_bytes, int num_splits, void* stream);
+
+/* Merge of split-KV partial states (replaces _fwd_kernel_stage2, decode_attention.py:497-557,
+ * and merge_state_v2, sgl-kernel/csrc/attention/merge_attn_states.cu): exposed for tests.
+ *   part_o   fp32 [bs, Hq, num_splits, Dv] ; part_lse fp32 [bs, Hq, num_splits] (log2 domain)  */
+/* Request b owns splits of split_chunk = round_up(ceil(len_b / num_splits), split_align) tokens;
+ * only the first ceil(len_b / split_chunk) partials are read.                                  */
+int b200_attn_decode_split_align(int D, int group);
+int b200_attn_merge(const float* part_o, const float* part_lse, void* o, int64_t o_stride,
+                    const int64_t* seq_lens, int bs, int Hq, int Dv, int num_splits,
+                    int split_align, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_HOTPATH_H_ */

@@ -1,0 +1,17 @@
+"""oracle/ — TEST INFRASTRUCTURE ONLY.
+
+CPU restatements of the reference's algorithms for the hot path.  Only
+`tests/`, `__graft_entry__.smoke()` and `bench.py`'s cpu_baseline / `--impl reference` legs may
+import this package, and only as the checker or the timed CPU baseline — never as (part of) the
+product path.  Nothing under `sglang_security_b200/` imports it.
+
+Pinning status (details in DESIGN.md §3):
+  attention decode/extend : pinned — checked against outputs of the reference's own
+      torch_native_backend.py run in the authoring container (tests/golden/attn_*.pt, generated
+      by oracle/gen_golden.py) and against the reference sgl-kernel CPU kernels (oracle/_ref).
+  pools / kv-indices      : pinned by the same fixtures (bit-exact) and the reference test's
+      python-loop definition (test/srt/test_create_kvindices.py:40-49).
+  FP8 quant / GEMM, AWQ   : restatements of the torch references inside the reference's tests
+      (file:line in each function); pinned by fixtures generated from those test files.
+  GPTQ                    : parity unpinned (arithmetic lives in vllm 0.8.4, absent).
+"""

@@ -1,0 +1,106 @@
+"""ctypes binding of libb200hotpath.so (the C-ABI declared in include/b200_hotpath.h).
+
+There is deliberately NO fallback: if the shared library is missing or a call returns a
+non-zero status this module raises.  The product path never routes through a CPU or
+PyTorch-eager substitute.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p
+from pathlib import Path
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libb200hotpath.so"
+_lib = None
+
+# dtype codes (enum b200_dtype)
+BF16, F16, F32, FP8_E4M3 = 0, 1, 2, 3
+
+_SIGNATURES = {
+    "b200_version": (c_int, []),
+    "b200_last_error": (c_char_p, []),
+    "b200_launch_count": (c_int64, []),
+    "b200_timing_enable": (c_int, [c_int]),
+    "b200_timing_read": (c_int, [c_char_p, ctypes.POINTER(c_int64), ctypes.POINTER(ctypes.c_double)]),
+    "b200_kv_write": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+                              c_int, c_int, c_int, c_void_p]),
+    "b200_kv_indices": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_void_p, c_int, c_void_p]),
+    "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_attn_decode_num_splits": (c_int, [c_int, c_int, c_int, c_int, c_int64, c_int]),
+    "b200_attn_decode_split_align": (c_int, [c_int, c_int]),
+    "b200_attn_decode": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                 c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
+                                 c_int, c_int, c_int, c_float, c_float, c_int, c_void_p, c_size_t,
+                                 c_int, c_void_p]),
+    "b200_attn_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int,
+                                c_int, c_int, c_int, c_int, c_void_p]),
+}
+
+
+class B200Error(RuntimeError):
+    """Raised when a b200_* entry point reports a non-zero status."""
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def exported_symbols():
+    return list(_SIGNATURES)
+
+
+def load():
+    """Load the shared library once; raise if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise B200Error(
+            f"{_LIB_PATH} is missing: build it with `python -m sglang_security_b200.build` "
+            "(there is no CPU / eager fallback for the hot path)")
+    lib = ctypes.CDLL(str(_LIB_PATH))
+    for name, (restype, argtypes) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so is stale: fail loudly
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        msg = load().b200_last_error()
+        raise B200Error(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def timing_enable(on: bool) -> None:
+    load().b200_timing_enable(1 if on else 0)
+
+
+def timing_read(name: str = ""):
+    """-> (launches, total_ms) of the timed launches of kernel `name` since the last read."""
+    n, ms = c_int64(0), ctypes.c_double(0.0)
+    load().b200_timing_read(name.encode(), ctypes.byref(n), ctypes.byref(ms))
+    return n.value, ms.value
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def dtype_code(torch_dtype) -> int:
+    import torch
+
+    table = {torch.bfloat16: BF16, torch.float16: F16, torch.float32: F32,
+             torch.float8_e4m3fn: FP8_E4M3}
+    if torch_dtype not in table:
+        raise B200Error(f"dtype {torch_dtype} is not supported by the B200 hot path")
+    return table[torch_dtype]
+
+
+def current_stream() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

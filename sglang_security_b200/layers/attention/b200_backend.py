@@ -1,0 +1,176 @@
+"""B200AttnBackend — the single new AttentionBackend of the hot path.
+
+Drop-in for the reference backends (TorchNativeAttnBackend is the numerical oracle,
+python/sglang/srt/layers/attention/torch_native_backend.py:17-270; TritonAttnBackend the GPU
+implementation of the same interface, triton_backend.py:151-835).  It indexes
+`req_to_token_pool.req_to_token` and the `MHATokenToKVPool` buffers in place (layouts unchanged)
+and calls the sm_100a kernels through the C-ABI (include/b200_hotpath.h):
+
+  forward_decode : b200_kv_write -> b200_attn_decode (split-KV gather kernel + merge kernel)
+  forward_extend : b200_kv_write -> b200_attn_extend (tcgen05 prefix rectangle + causal triangle)
+
+All per-step metadata is computed without a device->host sync; buffers are persistent so the
+decode step can be captured in a CUDA graph.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from ... import _lib
+from ...mem_cache.memory_pool import kv_write
+from .base_attn_backend import AttentionBackend
+
+
+@dataclass
+class ForwardMetadata:
+    num_splits: int = 1
+    workspace: Optional[torch.Tensor] = None
+    # extend only
+    qo_indptr: Optional[torch.Tensor] = None
+    max_extend_len: int = 0
+    total_extend: int = 0
+
+
+def _as_i64(t: torch.Tensor) -> torch.Tensor:
+    return t if t.dtype == torch.int64 else t.to(torch.int64)
+
+
+class B200AttnBackend(AttentionBackend):
+    def __init__(self, model_runner, skip_prefill: bool = False):
+        super().__init__()
+        self.lib = _lib.load()  # raises if the CUDA library has not been built
+        self.device = model_runner.device
+        self.req_to_token = model_runner.req_to_token_pool.req_to_token
+        tp = getattr(model_runner, "tp_size", 1)
+        cfg = model_runner.model_config
+        self.num_head = cfg.num_attention_heads // tp
+        self.num_kv_head = cfg.get_num_kv_heads(tp)
+        self.max_context_len = cfg.context_len
+        self.skip_prefill = skip_prefill
+        server_args = getattr(model_runner, "server_args", None)
+        # 0 -> heuristic; otherwise a fixed split count (same knob as
+        # --triton-attention-num-kv-splits, server_args.py:195)
+        self.fixed_num_kv_splits = int(getattr(server_args, "b200_attention_num_kv_splits", 0) or 0)
+        self.v_head_dim = model_runner.token_to_kv_pool.get_value_buffer(0).shape[-1]
+        self.num_sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.forward_metadata: Optional[ForwardMetadata] = None
+        self._workspace: Optional[torch.Tensor] = None
+        self._graph_workspace: Optional[torch.Tensor] = None
+        self._graph_max_bs = 0
+
+    # ------------------------------------------------------------------ metadata
+    def _num_splits(self, bs: int, head_dim: int, avg_len: int) -> int:
+        if self.fixed_num_kv_splits > 0:
+            return self.fixed_num_kv_splits
+        return self.lib.b200_attn_decode_num_splits(
+            bs, self.num_kv_head, self.num_head // self.num_kv_head, head_dim, int(avg_len),
+            self.num_sms)
+
+    def _ensure_workspace(self, bs: int, num_splits: int) -> Optional[torch.Tensor]:
+        need = self.lib.b200_attn_decode_workspace_bytes(bs, self.num_head, self.v_head_dim,
+                                                         num_splits)
+        if need == 0:
+            return None
+        if self._workspace is None or self._workspace.numel() < need:
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._workspace
+
+    def init_forward_metadata(self, forward_batch):
+        bs = forward_batch.batch_size
+        if forward_batch.forward_mode.is_decode_or_idle():
+            if bs == 0:
+                self.forward_metadata = ForwardMetadata()
+                return
+            total = forward_batch.seq_lens_sum or bs * self.max_context_len
+            head_dim = self.v_head_dim
+            s = self._num_splits(bs, head_dim, max(1, total // bs))
+            self.forward_metadata = ForwardMetadata(num_splits=s,
+                                                    workspace=self._ensure_workspace(bs, s))
+        else:
+            self.forward_metadata = self._init_extend_metadata(forward_batch)
+
+    def _init_extend_metadata(self, forward_batch) -> ForwardMetadata:
+        raise NotImplementedError("B200AttnBackend.forward_extend is not built yet")
+
+    # ------------------------------------------------------------------ CUDA graph hooks
+    def init_cuda_graph_state(self, max_bs: int):
+        self._graph_max_bs = max_bs
+        max_splits = 64
+        need = self.lib.b200_attn_decode_workspace_bytes(max_bs, self.num_head, self.v_head_dim,
+                                                         max_splits)
+        self._graph_workspace = torch.empty(max(need, 16), dtype=torch.uint8, device=self.device)
+
+    def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens,
+                                                 encoder_lens, forward_mode, spec_info):
+        if not forward_mode.is_decode_or_idle():
+            raise ValueError(f"B200AttnBackend: cuda graph capture of {forward_mode!r} unsupported")
+        if spec_info is not None:
+            raise NotImplementedError("speculative decoding is outside the B200 hot-path scope")
+        # The split count is frozen into the captured launch: choose it for a nominal context.
+        s = min(64, self._num_splits(bs, self.v_head_dim, min(self.max_context_len, 4096)))
+        self.forward_metadata = ForwardMetadata(num_splits=s, workspace=self._graph_workspace)
+
+    def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum,
+                                                encoder_lens, forward_mode, spec_info,
+                                                seq_lens_cpu):
+        # Nothing to refresh: the decode kernel reads req_to_token / seq_lens directly, so there
+        # is no derived index buffer to rebuild and no host sync.
+        return
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        return 1
+
+    # ------------------------------------------------------------------ forward
+    def _save_kv(self, layer, forward_batch, k, v):
+        pool = forward_batch.token_to_kv_pool
+        k_cache = pool.get_key_buffer(layer.layer_id)
+        v_cache = pool.get_value_buffer(layer.layer_id)
+        if k.dtype != k_cache.dtype:
+            # quantised KV cache (FP8): scaling/cast order is owned by the pool
+            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, layer.k_scale,
+                               layer.v_scale)
+        else:
+            kv_write(k, v, k_cache, v_cache, forward_batch.out_cache_loc)
+        return k_cache, v_cache
+
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
+        d, dv = layer.qk_head_dim, layer.v_head_dim
+        q = q.reshape(-1, hq * d)
+        if q.stride(-1) != 1:
+            q = q.contiguous()
+        bs = q.shape[0]
+        o = q.new_empty((bs, hq * dv))
+        pool = forward_batch.token_to_kv_pool
+        if save_kv_cache:
+            k_cache, v_cache = self._save_kv(layer, forward_batch, k, v)
+        else:
+            k_cache = pool.get_key_buffer(layer.layer_id)
+            v_cache = pool.get_value_buffer(layer.layer_id)
+        if bs == 0:
+            return o
+        if k_cache.dtype != q.dtype:
+            raise _lib.B200Error(
+                f"B200AttnBackend.forward_decode: KV cache dtype {k_cache.dtype} != q dtype "
+                f"{q.dtype} (FP8 KV cache is a later row of the scope table)")
+        md = self.forward_metadata
+        req_to_token = forward_batch.req_to_token_pool.req_to_token
+        ws = md.workspace
+        rc = self.lib.b200_attn_decode(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
+            _as_i64(forward_batch.req_pool_indices).data_ptr(),
+            _as_i64(forward_batch.seq_lens).data_ptr(), bs, hq, hkv, d, dv,
+            float(layer.scaling), float(layer.logit_cap or 0.0), _lib.dtype_code(q.dtype),
+            _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits, _lib.current_stream())
+        _lib.check(rc, "b200_attn_decode")
+        return o
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        raise NotImplementedError("B200AttnBackend.forward_extend is not built yet")
+
+    def support_triton(self):
+        return False

@@ -1,0 +1,61 @@
+"""CPU tests of the C-ABI boundary: the library builds for sm_100a, loads, and exports every
+symbol include/b200_hotpath.h declares.  No compute call is made (no GPU here)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib_path():
+    from sglang_security_b200 import build
+
+    return build.build()
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "b200_hotpath.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported(lib_path):
+    lib = ctypes.CDLL(str(lib_path))
+    declared = _declared_symbols()
+    assert len(declared) >= 8
+    missing = [s for s in declared if not hasattr(lib, s)]
+    assert not missing, f"declared in the header but not exported: {missing}"
+
+
+def test_python_binding_covers_header(lib_path):
+    from sglang_security_b200 import _lib
+
+    assert sorted(_lib.exported_symbols()) == _declared_symbols()
+    lib = _lib.load()
+    assert lib.b200_version() >= 1
+    assert lib.b200_launch_count() >= 0
+
+
+def test_host_side_helpers_need_no_gpu(lib_path):
+    from sglang_security_b200 import _lib
+
+    lib = _lib.load()
+    # pure host functions: workspace sizing and the split heuristic
+    assert lib.b200_attn_decode_workspace_bytes(64, 32, 128, 1) == 0
+    assert lib.b200_attn_decode_workspace_bytes(64, 32, 128, 4) == 64 * 32 * 4 * (128 + 1) * 4
+    s = lib.b200_attn_decode_num_splits(64, 8, 4, 128, 4096, 148)
+    assert 1 <= s <= 64
+    assert lib.b200_attn_decode_num_splits(1, 8, 4, 128, 100, 148) == 1
+    assert lib.b200_attn_decode_split_align(128, 4) == 64
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from sglang_security_b200 import _lib
+
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "_LIB_PATH", tmp_path / "nope.so")
+    with pytest.raises(_lib.B200Error):
+        _lib.load()
