@@ -100,6 +100,46 @@ int b200_attn_merge(const float* part_o, const float* part_lse, void* o, int64_t
                     const int64_t* seq_lens, int bs, int Hq, int Dv, int num_splits,
                     int split_align, int dtype, void* stream);
 
+/* ---- FP8 activation quantisation ----------------------------------------- */
+/* Per-token dynamic (static_scale == NULL): scales[m] = absmax(x[m,:]) / 448, q = sat(x * (1/scale))
+ *   replaces sgl_per_token_quant_fp8 (sgl-kernel/csrc/gemm/per_token_quant_fp8.cu:9-106).
+ * use_division != 0: scales[m] = max(absmax, eps) / 448, q = sat(x / scale) — the group_size == K
+ *   case of per_token_group_quant_fp8 used for load-time per-channel weight quant (fp8.py:340-343).
+ * static_scale != NULL: q = sat(x * (1 / *static_scale)), scales untouched
+ *   (replaces _static_quant_fp8, python/sglang/srt/layers/quantization/fp8_kernel.py:336-376).
+ * x [M,K] bf16/f16 row stride ldx; q [M,K] e4m3 row stride ldq; K % 8 == 0.                    */
+int b200_fp8_quant_per_token(const void* x, int64_t ldx, void* q, int64_t ldq, float* scales,
+                             const float* static_scale, int M, int K, int use_division, float eps,
+                             int dtype, void* stream);
+/* Per-(token, 128-group): scale = max(absmax, eps) / 448, q = sat(x / scale); replaces
+ * sgl_per_token_group_quant_fp8 (sgl-kernel/csrc/gemm/per_token_group_quant_8bit.cu:19-197).
+ * scales[m * scale_row_stride + g * scale_col_stride] (row-major, column-major or TMA-aligned
+ * layouts of fp8_kernel.py:218-238).                                                          */
+int b200_fp8_quant_group128(const void* x, int64_t ldx, void* q, int64_t ldq, float* scales,
+                            int64_t scale_row_stride, int64_t scale_col_stride, int M, int K,
+                            float eps, int dtype, void* stream);
+
+/* ---- FP8 W8A8 GEMM, per-token x per-channel scales (tcgen05) ---------------- */
+/* Replaces sgl_kernel.fp8_scaled_mm (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1071-1146):
+ *   out[M,N] = (A[M,K] . B[N,K]^T) * sa[m*sa_stride] * sb[n*sb_stride] (+ bias[n])
+ * A e4m3 row-major (lda), B e4m3 stored [N,K] K-contiguous (ldb) — i.e. the reference's
+ * column-major [K,N] weight view; sa/sb fp32 (stride 0 = per-tensor); bias/out bf16 or f16.      */
+int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                         int sa_stride, const float* sb, int sb_stride, const void* bias,
+                         void* out, int64_t ldc, int M, int N, int K, int out_dtype,
+                         void* stream);
+
+/* ---- FP8 block-scaled GEMM (128x128 weight blocks, 1x128 activation groups) -------- */
+/* Replaces fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:345-423) and
+ * w8a8_block_fp8_matmul (python/sglang/srt/layers/quantization/fp8_kernel.py:774-891):
+ *   out[m,n] = sum_kb (A[m,kb] . B[n,kb]^T) * as[m*as_row_stride + kb*as_col_stride]
+ *                                           * bs[(n/128)*bs_row_stride + kb]        (+ bias[n])
+ * A [M,K] e4m3 (lda), B [N,K] e4m3 (ldb), scales fp32, out bf16/f16.                         */
+int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ldb, const float* as,
+                           int64_t as_row_stride, int64_t as_col_stride, const float* bs,
+                           int64_t bs_row_stride, const void* bias, void* out, int64_t ldc, int M,
+                           int N, int K, int out_dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,96 @@
+// FP8 W8A8 GEMM with per-token x per-channel scales on tcgen05 (replaces sgl-kernel
+// fp8_scaled_mm, sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1071-1146, called from
+// apply_fp8_linear, python/sglang/srt/layers/quantization/fp8_utils.py:636-648):
+//   out[M,N] = (A_e4m3[M,K] . B_e4m3[N,K]^T) * sa[m] * sb[n] (+ bias[n])  -> bf16 / f16
+// plus the TMA-descriptor helper shared by every tcgen05 kernel of the library.
+#include "gemm_tc.cuh"
+
+namespace b200 {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                 uint64_t pitch_bytes, uint32_t box_rows, uint32_t box_cols, int elt_bytes,
+                 bool is_weight) {
+  EncodeTiledFn enc = get_encode_tiled();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15u) == 0 && pitch_bytes % 16 == 0,
+               "TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch "
+               "(pitch=%llu)", static_cast<unsigned long long>(pitch_bytes));
+  B200_REQUIRE(box_cols * elt_bytes == 128 && box_rows <= 256, "bad TMA box %ux%u", box_rows,
+               box_cols);
+  const CUtensorMapDataType dt = elt_bytes == 1   ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                 : elt_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16
+                                                  : CU_TENSOR_MAP_DATA_TYPE_UINT32;
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         is_weight ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                   : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" {
+
+int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                         int sa_stride, const float* sb, int sb_stride, const void* bias,
+                         void* out, int64_t ldc, int M, int N, int K, int out_dtype,
+                         void* stream) {
+  using namespace b200;
+  if (M == 0 || N == 0) return 0;
+  B200_REQUIRE(a && b && out, "b200_fp8_gemm_rowcol: null pointer");
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_fp8_gemm_rowcol: bad shape %dx%dx%d", M, N, K);
+  B200_REQUIRE(lda % 16 == 0 && ldb % 16 == 0 && aligned16(a) && aligned16(b),
+               "b200_fp8_gemm_rowcol: A/B must be 16-byte aligned with lda/ldb %% 16 == 0 "
+               "(same rule as the reference kernel, fp8_gemm_kernel.cu:1090-1097)");
+  B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F16,
+               "b200_fp8_gemm_rowcol: out dtype %d", out_dtype);
+  GemmEpilogueParams ep;
+  ep.out = out;
+  ep.ldc = ldc;
+  ep.sa = sa;
+  ep.sb = sb;
+  ep.sa_stride = sa_stride;
+  ep.sb_stride = sb_stride;
+  ep.bias = bias;
+  ep.M = M;
+  ep.N = N;
+  ep.K = K;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Tile choice: 128x256 when there is enough work to fill the SMs with it, else 128x128.
+  const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);
+  const bool big = tiles256 >= device_sm_count();
+  if (out_dtype == B200_BF16) {
+    return big ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm")
+               : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm");
+  }
+  return big ? launch_gemm_tn<kKindFp8, 256, 4, __half>(a, lda, b, ldb, ep, st, "fp8_gemm")
+             : launch_gemm_tn<kKindFp8, 128, 6, __half>(a, lda, b, ldb, ep, st, "fp8_gemm");
+}
+
+}  // extern "C"

@@ -45,11 +45,16 @@ __device__ __forceinline__ float block_max(float v, float* red) {
 }
 
 // One CTA per token row.  K % 8 == 0.
-template <typename T, bool STATIC>
+// MODE 0: dynamic, q = sat(x * (1/scale))           (per_token_quant_fp8.cu)
+// MODE 1: static scale, q = sat(x * (1/scale))      (_static_quant_fp8)
+// MODE 2: dynamic, scale = max(absmax, eps)/448, q = sat(x / scale): the group_size == K case of
+//         per_token_group_quant_fp8 used for load-time per-channel weight quantisation.
+template <typename T, int MODE>
 __global__ void __launch_bounds__(256)
 fp8_quant_per_token_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __restrict__ q,
                            int64_t ldq, float* __restrict__ scales,
-                           const float* __restrict__ static_scale, int K) {
+                           const float* __restrict__ static_scale, int K, float eps) {
+  constexpr bool STATIC = MODE == 1;
   __shared__ float red[32];
   const int m = blockIdx.x;
   const T* row = x + m * ldx;
@@ -67,6 +72,7 @@ fp8_quant_per_token_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __rest
       for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(f[e]));
     }
     amax = block_max(amax, red);
+    if (MODE == 2) amax = fmaxf(amax, eps);
     scale = amax / kFp8Max;
     if (threadIdx.x == 0) scales[m] = scale;
   }
@@ -78,9 +84,10 @@ fp8_quant_per_token_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __rest
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      lo |= static_cast<uint32_t>(to_e4m3(fmaxf(fminf(f[e] * inv, kFp8Max), -kFp8Max))) << (8 * e);
-      hi |= static_cast<uint32_t>(to_e4m3(fmaxf(fminf(f[4 + e] * inv, kFp8Max), -kFp8Max)))
-            << (8 * e);
+      const float a = MODE == 2 ? f[e] / scale : f[e] * inv;
+      const float b = MODE == 2 ? f[4 + e] / scale : f[4 + e] * inv;
+      lo |= static_cast<uint32_t>(to_e4m3(fmaxf(fminf(a, kFp8Max), -kFp8Max))) << (8 * e);
+      hi |= static_cast<uint32_t>(to_e4m3(fmaxf(fminf(b, kFp8Max), -kFp8Max))) << (8 * e);
     }
     *reinterpret_cast<uint2*>(out + i * 8) = make_uint2(lo, hi);
   }
@@ -129,7 +136,8 @@ fp8_quant_group128_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __restr
 extern "C" {
 
 int b200_fp8_quant_per_token(const void* x, int64_t ldx, void* q, int64_t ldq, float* scales,
-                             const float* static_scale, int M, int K, int dtype, void* stream) {
+                             const float* static_scale, int M, int K, int use_division, float eps,
+                             int dtype, void* stream) {
   using namespace b200;
   if (M == 0) return 0;
   B200_REQUIRE(x && q && (scales || static_scale), "b200_fp8_quant_per_token: null pointer");
@@ -142,16 +150,18 @@ int b200_fp8_quant_per_token(const void* x, int64_t ldx, void* q, int64_t ldq, f
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   ScopedKernelTimer timer("fp8_quant", st);
   const int threads = K >= 2048 ? 256 : 128;
-#define LAUNCH(T, S)                                                                           \
-  fp8_quant_per_token_kernel<T, S><<<M, threads, 0, st>>>(static_cast<const T*>(x), ldx,       \
-                                                          static_cast<uint8_t*>(q), ldq, scales, \
-                                                          static_scale, K)
+#define LAUNCH(T, MODE)                                                                          \
+  fp8_quant_per_token_kernel<T, MODE><<<M, threads, 0, st>>>(static_cast<const T*>(x), ldx,      \
+                                                             static_cast<uint8_t*>(q), ldq,      \
+                                                             scales, static_scale, K, eps)
   if (dtype == B200_BF16) {
-    if (static_scale) LAUNCH(__nv_bfloat16, true);
-    else LAUNCH(__nv_bfloat16, false);
+    if (static_scale) LAUNCH(__nv_bfloat16, 1);
+    else if (use_division) LAUNCH(__nv_bfloat16, 2);
+    else LAUNCH(__nv_bfloat16, 0);
   } else {
-    if (static_scale) LAUNCH(__half, true);
-    else LAUNCH(__half, false);
+    if (static_scale) LAUNCH(__half, 1);
+    else if (use_division) LAUNCH(__half, 2);
+    else LAUNCH(__half, 0);
   }
 #undef LAUNCH
   B200_CHECK_LAUNCH("fp8_quant_per_token_kernel");

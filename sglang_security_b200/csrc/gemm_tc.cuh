@@ -1,0 +1,282 @@
+// Persistent warp-specialised tcgen05 GEMM for sm_100a:  C[M,N] = epilogue( A[M,K] . B[N,K]^T )
+// Both operands are K-major ("TN"): A rows are tokens, B rows are output channels — exactly how the
+// reference stores activations and (transposed-view) weights (fp8.py:349,391; fp8_utils.py:636-648).
+//
+//   warp 0   : TMA producer   — cp.async.bulk.tensor 128-byte-swizzled A/B tiles into a STAGES ring
+//   warp 1   : MMA issuer     — one elected thread issues tcgen05.mma (M=128, N=BLOCK_N, K=32 B),
+//                               accumulators live in TMEM (2 x BLOCK_N fp32 columns, double buffered)
+//   warps 2-5: epilogue       — tcgen05.ld 32 lanes x 32 columns, scale / bias, cast, 16-byte stores
+// Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue) and the
+// static persistent tile schedule (tile = blockIdx.x + i * gridDim.x, M fastest so concurrently
+// running CTAs share the same weight tile through L2).
+#pragma once
+
+#include "tc_common.cuh"
+
+namespace b200 {
+
+enum GemmKind { kKindFp8 = 0, kKindBf16 = 1, kKindF16 = 2 };
+
+struct GemmEpilogueParams {
+  void* out;            // [M, N] OutT, row stride ldc
+  int64_t ldc;
+  const float* sa;      // per-row scale (stride sa_stride: 1 = per token, 0 = per tensor) or null
+  const float* sb;      // per-column scale (stride sb_stride) or null
+  int sa_stride, sb_stride;
+  const void* bias;     // [N] OutT or null
+  int M, N, K;
+};
+
+template <int KIND>
+struct GemmKindTraits;
+template <>
+struct GemmKindTraits<kKindFp8> {
+  static constexpr int ELT = 1;
+  static constexpr uint32_t FMT = 0;  // E4M3
+};
+template <>
+struct GemmKindTraits<kKindBf16> {
+  static constexpr int ELT = 2;
+  static constexpr uint32_t FMT = 1;  // BF16
+};
+template <>
+struct GemmKindTraits<kKindF16> {
+  static constexpr int ELT = 2;
+  static constexpr uint32_t FMT = 0;  // F16
+};
+
+template <int KIND, int BLOCK_N, int STAGES>
+struct GemmCfg {
+  static constexpr int BLOCK_M = 128;
+  static constexpr int ELT = GemmKindTraits<KIND>::ELT;
+  static constexpr int BLOCK_K = 128 / ELT;        // elements per 128-byte swizzle row
+  static constexpr int UMMA_K_BYTES = 32;
+  static constexpr int A_BYTES = BLOCK_M * 128;
+  static constexpr int B_BYTES = BLOCK_N * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int TMEM_COLS = 2 * BLOCK_N;    // power of two for BLOCK_N in {64,128,256}
+  static constexpr int THREADS = 192;
+  static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+  static_assert(BLOCK_N == 64 || BLOCK_N == 128 || BLOCK_N == 256, "BLOCK_N");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+};
+
+template <typename OutT>
+__device__ __forceinline__ uint32_t pack_out2(float a, float b);
+template <>
+__device__ __forceinline__ uint32_t pack_out2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+template <>
+__device__ __forceinline__ uint32_t pack_out2<__half>(float a, float b) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int KIND, int BLOCK_N, int STAGES, typename OutT>
+__global__ void __launch_bounds__(192, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmEpilogueParams ep) {
+  using C = GemmCfg<KIND, BLOCK_N, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B
+  const uint32_t bars = smem_base + STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
+      smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+
+  const int m_blocks = ceil_div(ep.M, C::BLOCK_M);
+  const int n_blocks = ceil_div(ep.N, BLOCK_N);
+  const int num_tiles = m_blocks * n_blocks;
+  const int num_kb = ceil_div(ep.K, C::BLOCK_K);
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tmap(&tmap_a);
+    tc::prefetch_tmap(&tmap_b);
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(full_bar(s), 1);
+      tc::mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(tfull_bar(a), 1);
+      tc::mbar_init(tempty_bar(a), 4);  // one arrive per epilogue warp
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) {
+    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc::tmem_relinquish();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(empty_bar(stage), phase ^ 1u);
+          tc::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+          tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * C::BLOCK_K, m_blk * C::BLOCK_M);
+          tc::tma_load_2d(sa + C::A_BYTES, &tmap_b, full_bar(stage), kb * C::BLOCK_K,
+                          n_blk * BLOCK_N);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(GemmKindTraits<KIND>::FMT, GemmKindTraits<KIND>::FMT,
+                                                C::BLOCK_M, BLOCK_N, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+        const int acc = local & 1;
+        const uint32_t acc_phase = (local >> 1) & 1u;
+        tc::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);  // epilogue drained this accumulator
+        tc::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(full_bar(stage), phase);
+          tc::tc_fence_after();
+          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sb = sa + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < 128 / C::UMMA_K_BYTES; ++k) {
+            const uint64_t adesc = tc::make_smem_desc_sw128(sa + k * C::UMMA_K_BYTES, 1024, 16);
+            const uint64_t bdesc = tc::make_smem_desc_sw128(sb + k * C::UMMA_K_BYTES, 1024, 16);
+            if (KIND == kKindFp8)
+              tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            else
+              tc::mma_f16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          tc::mma_commit(empty_bar(stage));  // smem slot free once these MMAs have read it
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        tc::mma_commit(tfull_bar(acc));  // accumulator complete
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    OutT* out = static_cast<OutT*>(ep.out);
+    const OutT* bias = static_cast<const OutT*>(ep.bias);
+    int local = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+      const int acc = local & 1;
+      const uint32_t acc_phase = (local >> 1) & 1u;
+      tc::mbar_wait(tfull_bar(acc), acc_phase);
+      tc::tc_fence_after();
+      const int row = m_blk * C::BLOCK_M + quarter * 32 + lane;
+      const bool row_ok = row < ep.M;
+      const float sa = (ep.sa && row_ok) ? __ldg(ep.sa + static_cast<int64_t>(row) * ep.sa_stride)
+                                         : 1.0f;
+      OutT* orow = out + static_cast<int64_t>(row) * ep.ldc;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t r[32];
+        const uint32_t taddr =
+            tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + c * 32;
+        tc::tmem_ld32(taddr, r);
+        tc::tmem_ld_wait();
+        const int col0 = n_blk * BLOCK_N + c * 32;
+        if (row_ok && col0 < ep.N) {
+          if (col0 + 32 <= ep.N && (ep.ldc & 7) == 0) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {  // 4 x 16-byte stores of 8 outputs
+              uint32_t packed[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int j = v * 8 + e * 2;
+                float x0 = __uint_as_float(r[j]), x1 = __uint_as_float(r[j + 1]);
+                float s0 = sa, s1 = sa;
+                if (ep.sb) {
+                  s0 *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
+                  s1 *= __ldg(ep.sb + static_cast<int64_t>(col0 + j + 1) * ep.sb_stride);
+                }
+                float b0 = 0.f, b1 = 0.f;
+                if (bias) {
+                  b0 = to_float<OutT>(bias[col0 + j]);
+                  b1 = to_float<OutT>(bias[col0 + j + 1]);
+                }
+                packed[e] = pack_out2<OutT>(fmaf(x0, s0, b0), fmaf(x1, s1, b1));
+              }
+              *reinterpret_cast<uint4*>(orow + col0 + v * 8) =
+                  make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (col0 + j >= ep.N) break;
+              float s = sa;
+              if (ep.sb) s *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
+              const float b = bias ? to_float<OutT>(bias[col0 + j]) : 0.f;
+              orow[col0 + j] = from_float<OutT>(fmaf(__uint_as_float(r[j]), s, b));
+            }
+          }
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
+}
+
+// Host launcher: builds the two TMA descriptors and launches one CTA per SM (or per tile).
+template <int KIND, int BLOCK_N, int STAGES, typename OutT>
+int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
+                   const GemmEpilogueParams& ep, cudaStream_t st, const char* timer_name) {
+  using C = GemmCfg<KIND, BLOCK_N, STAGES>;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d(&ta, a, ep.M, ep.K, lda * C::ELT, C::BLOCK_M, C::BLOCK_K, C::ELT, false);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tb, b, ep.N, ep.K, ldb * C::ELT, BLOCK_N, C::BLOCK_K, C::ELT, true);
+  if (rc) return rc;
+  auto kern = gemm_tn_kernel<KIND, BLOCK_N, STAGES, OutT>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+    attr_done = true;
+  }
+  const int tiles = ceil_div(ep.M, C::BLOCK_M) * ceil_div(ep.N, BLOCK_N);
+  const int sms = device_sm_count();
+  const int grid = tiles < sms ? tiles : sms;
+  {
+    ScopedKernelTimer timer(timer_name, st);
+    kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(ta, tb, ep);
+  }
+  B200_CHECK_LAUNCH("gemm_tn_kernel");
+  return 0;
+}
+
+}  // namespace b200

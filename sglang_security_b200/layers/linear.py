@@ -1,0 +1,178 @@
+"""Linear layers with the reference's structure (python/sglang/srt/layers/linear.py): the quant
+method owns the weights and the math (`quant_method.apply(layer, x, bias)`), column-parallel layers
+shard N, row-parallel layers shard K and all-reduce their partial outputs (linear.py:1277-1299;
+bias only on rank 0, :1290).  Weight loaders slice checkpoints by tp_rank (linear.py:352-358, 1184).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.nn.functional as F
+from torch.nn import Parameter
+
+from ..distributed.parallel_state import (get_tensor_model_parallel_rank,
+                                          get_tensor_model_parallel_world_size,
+                                          tensor_model_parallel_all_gather,
+                                          tensor_model_parallel_all_reduce)
+from .quantization.base_config import LinearMethodBase, QuantizationConfig, set_weight_attrs
+
+
+def divide(a: int, b: int) -> int:
+    if a % b != 0:
+        raise ValueError(f"{a} is not divisible by {b}")
+    return a // b
+
+
+class UnquantizedLinearMethod(LinearMethodBase):
+    """16-bit weights: plain library GEMM (cuBLAS through torch), as in the reference
+    (linear.py:143-176).  Not part of the quantised hot path."""
+
+    def create_weights(self, layer, input_size_per_partition, output_partition_sizes, input_size,
+                       output_size, params_dtype, **extra_weight_attrs):
+        extra_weight_attrs.pop("tp_size", None)
+        weight = Parameter(torch.empty(sum(output_partition_sizes), input_size_per_partition,
+                                       dtype=params_dtype), requires_grad=False)
+        set_weight_attrs(weight, {"input_dim": 1, "output_dim": 0})
+        layer.register_parameter("weight", weight)
+        set_weight_attrs(weight, extra_weight_attrs)
+
+    def apply(self, layer, x, bias=None):
+        return F.linear(x, layer.weight, bias)
+
+
+class LinearBase(torch.nn.Module):
+    def __init__(self, input_size: int, output_size: int, skip_bias_add: bool = False,
+                 params_dtype: Optional[torch.dtype] = None,
+                 quant_config: Optional[QuantizationConfig] = None, prefix: str = ""):
+        super().__init__()
+        self.input_size = input_size
+        self.output_size = output_size
+        self.skip_bias_add = skip_bias_add
+        self.params_dtype = params_dtype or torch.get_default_dtype()
+        self.quant_method = (UnquantizedLinearMethod() if quant_config is None
+                             else quant_config.get_quant_method(self, prefix=prefix))
+        self.prefix = prefix
+
+    def forward(self, x):
+        raise NotImplementedError()
+
+
+class ColumnParallelLinear(LinearBase):
+    def __init__(self, input_size: int, output_size: int, bias: bool = True,
+                 gather_output: bool = False, skip_bias_add: bool = False,
+                 params_dtype: Optional[torch.dtype] = None,
+                 quant_config: Optional[QuantizationConfig] = None,
+                 output_sizes: Optional[List[int]] = None, prefix: str = "",
+                 tp_rank: Optional[int] = None, tp_size: Optional[int] = None):
+        super().__init__(input_size, output_size, skip_bias_add, params_dtype, quant_config, prefix)
+        self.gather_output = gather_output
+        self.tp_rank = get_tensor_model_parallel_rank() if tp_rank is None else tp_rank
+        self.tp_size = get_tensor_model_parallel_world_size() if tp_size is None else tp_size
+        self.output_size_per_partition = divide(output_size, self.tp_size)
+        self.output_partition_sizes = [self.output_size_per_partition]
+        if output_sizes is not None:  # fused layers (qkv / gate_up): one logical width per shard
+            self.output_partition_sizes = [divide(s, self.tp_size) for s in output_sizes]
+        self.quant_method.create_weights(
+            layer=self, input_size_per_partition=input_size,
+            output_partition_sizes=self.output_partition_sizes, input_size=input_size,
+            output_size=output_size, params_dtype=self.params_dtype,
+            weight_loader=self.weight_loader, tp_size=self.tp_size)
+        if bias:
+            self.bias = Parameter(torch.zeros(self.output_size_per_partition, dtype=self.params_dtype),
+                                  requires_grad=False)
+            set_weight_attrs(self.bias, {"output_dim": 0, "weight_loader": self.weight_loader})
+        else:
+            self.register_parameter("bias", None)
+
+    def weight_loader(self, param: Parameter, loaded_weight: torch.Tensor):
+        output_dim = getattr(param, "output_dim", None)
+        if output_dim is not None and loaded_weight.shape[output_dim] != param.shape[output_dim]:
+            shard = param.shape[output_dim]
+            loaded_weight = loaded_weight.narrow(output_dim, self.tp_rank * shard, shard)
+        if loaded_weight.dim() == 0:
+            loaded_weight = loaded_weight.reshape(1)
+        assert param.shape == loaded_weight.shape, (param.shape, loaded_weight.shape)
+        param.data.copy_(loaded_weight)
+
+    def forward(self, input_):
+        bias = self.bias if not self.skip_bias_add else None
+        output = self.quant_method.apply(self, input_, bias)
+        if self.gather_output:
+            output = tensor_model_parallel_all_gather(output)
+        return output, (self.bias if self.skip_bias_add else None)
+
+
+class MergedColumnParallelLinear(ColumnParallelLinear):
+    """Several column-parallel projections fused along N (gate_up_proj)."""
+
+    def __init__(self, input_size: int, output_sizes: List[int], bias: bool = True, **kw):
+        self.output_sizes = output_sizes
+        super().__init__(input_size, sum(output_sizes), bias=bias, output_sizes=output_sizes, **kw)
+
+
+class QKVParallelLinear(ColumnParallelLinear):
+    """Fused q/k/v projection; q heads / tp, kv heads max(1, Hkv // tp) (replicated when tp > Hkv),
+    as models/llama.py:119-132."""
+
+    def __init__(self, hidden_size: int, head_size: int, total_num_heads: int,
+                 total_num_kv_heads: Optional[int] = None, bias: bool = True, **kw):
+        tp_size = kw.get("tp_size") or get_tensor_model_parallel_world_size()
+        self.hidden_size, self.head_size = hidden_size, head_size
+        self.total_num_heads = total_num_heads
+        self.total_num_kv_heads = total_num_kv_heads or total_num_heads
+        self.num_heads = divide(total_num_heads, tp_size)
+        if tp_size >= self.total_num_kv_heads:
+            self.num_kv_heads, self.num_kv_head_replicas = 1, divide(tp_size, self.total_num_kv_heads)
+        else:
+            self.num_kv_heads, self.num_kv_head_replicas = divide(self.total_num_kv_heads, tp_size), 1
+        out = (self.num_heads + 2 * self.num_kv_heads) * tp_size * head_size
+        sizes = [self.num_heads * head_size * tp_size, self.num_kv_heads * head_size * tp_size,
+                 self.num_kv_heads * head_size * tp_size]
+        super().__init__(hidden_size, out, bias=bias, output_sizes=sizes, **kw)
+
+
+class RowParallelLinear(LinearBase):
+    def __init__(self, input_size: int, output_size: int, bias: bool = True,
+                 input_is_parallel: bool = True, skip_bias_add: bool = False,
+                 params_dtype: Optional[torch.dtype] = None, reduce_results: bool = True,
+                 quant_config: Optional[QuantizationConfig] = None, prefix: str = "",
+                 tp_rank: Optional[int] = None, tp_size: Optional[int] = None):
+        super().__init__(input_size, output_size, skip_bias_add, params_dtype, quant_config, prefix)
+        self.input_is_parallel = input_is_parallel
+        self.reduce_results = reduce_results
+        self.tp_rank = get_tensor_model_parallel_rank() if tp_rank is None else tp_rank
+        self.tp_size = get_tensor_model_parallel_world_size() if tp_size is None else tp_size
+        self.input_size_per_partition = divide(input_size, self.tp_size)
+        self.quant_method.create_weights(
+            layer=self, input_size_per_partition=self.input_size_per_partition,
+            output_partition_sizes=[output_size], input_size=input_size, output_size=output_size,
+            params_dtype=self.params_dtype, weight_loader=self.weight_loader, tp_size=self.tp_size)
+        if not reduce_results and bias and not skip_bias_add:
+            raise ValueError("When not reduce the results, adding bias to the results can lead to "
+                             "incorrect results")
+        if bias:
+            self.bias = Parameter(torch.zeros(output_size, dtype=self.params_dtype),
+                                  requires_grad=False)
+        else:
+            self.register_parameter("bias", None)
+
+    def weight_loader(self, param: Parameter, loaded_weight: torch.Tensor):
+        input_dim = getattr(param, "input_dim", None)
+        if input_dim is not None and loaded_weight.shape[input_dim] != param.shape[input_dim]:
+            shard = param.shape[input_dim]
+            loaded_weight = loaded_weight.narrow(input_dim, self.tp_rank * shard, shard)
+        if loaded_weight.dim() == 0:
+            loaded_weight = loaded_weight.reshape(1)
+        assert param.shape == loaded_weight.shape, (param.shape, loaded_weight.shape)
+        param.data.copy_(loaded_weight)
+
+    def forward(self, input_):
+        if not self.input_is_parallel:
+            input_ = input_.chunk(self.tp_size, dim=-1)[self.tp_rank].contiguous()
+        # bias is fused into the GEMM only on rank 0 so the all-reduce adds it exactly once
+        bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
+        output = self.quant_method.apply(self, input_, bias=bias_)
+        if self.reduce_results and self.tp_size > 1:
+            output = tensor_model_parallel_all_reduce(output)
+        return output, (self.bias if self.skip_bias_add else None)

@@ -1,0 +1,65 @@
+"""FP8 linear glue: activation quantisation + scaled GEMM, mirroring
+python/sglang/srt/layers/quantization/fp8_utils.py (apply_fp8_linear :454-693,
+apply_w8a8_block_fp8_linear :152-304) and quantization/utils.py:68-88 (convert_to_channelwise).
+Only the sm_100a tcgen05 kernels are dispatched — no cuBLASLt / Triton / DeepGEMM alternatives."""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from .fp8_kernel import (fp8_blockwise_scaled_mm, fp8_scaled_mm, per_token_group_quant_fp8,
+                         sglang_per_token_quant_fp8, static_quant_fp8)
+
+
+def convert_to_channelwise(weight_scale: torch.Tensor, logical_widths: List[int]) -> torch.Tensor:
+    """Per-partition (fused qkv / gate_up shard) scales -> one scale per output channel [N, 1]."""
+    total = sum(logical_widths)
+    if weight_scale.dim() == 0:
+        return weight_scale.reshape(1, 1).expand(total, 1).to(torch.float32).contiguous()
+    widths = torch.tensor(logical_widths, device=weight_scale.device)
+    return torch.repeat_interleave(weight_scale.to(torch.float32), widths).reshape(total, 1)
+
+
+def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
+                     input_scale: Optional[torch.Tensor] = None,
+                     input_scale_ub: Optional[torch.Tensor] = None,
+                     bias: Optional[torch.Tensor] = None, cutlass_fp8_supported: bool = True,
+                     use_per_token_if_dynamic: bool = False) -> torch.Tensor:
+    """weight is the [K, N] column-major view of the e4m3 [N, K] weight; weight_scale has one
+    entry per output channel (or is a scalar)."""
+    input_2d = input.reshape(-1, input.shape[-1])
+    if input_2d.stride(-1) != 1:
+        input_2d = input_2d.contiguous()
+    output_shape = [*input.shape[:-1], weight.shape[1]]
+    if input_scale is not None:
+        qinput, x_scale = static_quant_fp8(input_2d, input_scale, repeat_scale=False)
+    else:
+        qinput, x_scale = sglang_per_token_quant_fp8(input_2d)
+    if weight_scale.numel() not in (1, weight.shape[1]):
+        raise ValueError("B200 fp8 linear supports per-channel (or per-tensor) weight scales only")
+    output = fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)
+    return output.view(*output_shape)
+
+
+def apply_w8a8_block_fp8_linear(input: torch.Tensor, weight: torch.Tensor, block_size: List[int],
+                                weight_scale: torch.Tensor,
+                                input_scale: Optional[torch.Tensor] = None,
+                                bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Block-quantised linear: weight [N, K] e4m3 with [ceil(N/128), ceil(K/128)] fp32 scales,
+    activations quantised per (token, 128-group) on the fly."""
+    assert input_scale is None
+    if list(block_size) != [128, 128]:
+        raise ValueError(f"B200 block-fp8 linear supports 128x128 weight blocks, got {block_size}")
+    input_2d = input.reshape(-1, input.shape[-1])
+    if input_2d.stride(-1) != 1:
+        input_2d = input_2d.contiguous()
+    output_shape = [*input.shape[:-1], weight.shape[0]]
+    q_input, x_scale = per_token_group_quant_fp8(input_2d, block_size[1], column_major_scales=False)
+    output = fp8_blockwise_scaled_mm(q_input, weight, x_scale, weight_scale, out_dtype=input.dtype,
+                                     bias=bias)
+    return output.view(*output_shape)
+
+
+def dispatch_w8a8_block_fp8_linear():
+    return apply_w8a8_block_fp8_linear
