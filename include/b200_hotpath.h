@@ -100,6 +100,23 @@ int b200_attn_merge(const float* part_o, const float* part_lse, void* o, int64_t
                     const int64_t* seq_lens, int bs, int Hq, int Dv, int num_splits,
                     int split_align, int dtype, void* stream);
 
+/* ---- extend (prefill with cached radix prefix) attention, tcgen05 -------------- */
+/* Replaces AttentionBackend.forward_extend's kernel (oracle torch_native_backend.py:27-110; GPU
+ * reference extend_attention_fwd, triton_ops/extend_attention.py:306-438).  For request b the
+ * extend_seq_lens[b] new tokens (rows extend_start_loc[b].. of q / o) attend to keys
+ *   slot(b,t) = req_to_token[req_pool_indices[b], t],  t <= extend_prefix_lens[b] + i   (causal)
+ * all gathered from the pool (the new tokens' K/V must already be written, as torch_native does).
+ * q [T, Hq, D] token stride q_stride; o [T, Hq, Dv] token stride o_stride; D == Dv in {64, 128}.
+ * max_extend_len = max_b extend_seq_lens[b] (host value, sizes the grid).                       */
+int b200_attn_extend(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                     int64_t kv_row_stride, void* o, int64_t o_stride,
+                     const int32_t* req_to_token, int64_t req_to_token_stride,
+                     const int64_t* req_pool_indices, const int64_t* seq_lens,
+                     const int32_t* extend_prefix_lens, const int32_t* extend_seq_lens,
+                     const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv,
+                     int D, int Dv, float scale, float logit_cap, int causal, int dtype,
+                     void* stream);
+
 /* ---- FP8 activation quantisation ----------------------------------------- */
 /* Per-token dynamic (static_scale == NULL): scales[m] = absmax(x[m,:]) / 448, q = sat(x * (1/scale))
  *   replaces sgl_per_token_quant_fp8 (sgl-kernel/csrc/gemm/per_token_quant_fp8.cu:9-106).

@@ -35,6 +35,10 @@ _SIGNATURES = {
                                  c_int, c_void_p]),
     "b200_attn_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int,
                                 c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_attn_extend": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
+                                 c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_float,
+                                 c_float, c_int, c_int, c_void_p]),
     "b200_fp8_quant_per_token": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
                                          c_int, c_int, c_int, c_float, c_int, c_void_p]),
     "b200_fp8_quant_group128": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,

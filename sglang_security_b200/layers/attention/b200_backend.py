@@ -93,7 +93,22 @@ class B200AttnBackend(AttentionBackend):
             self.forward_metadata = self._init_extend_metadata(forward_batch)
 
     def _init_extend_metadata(self, forward_batch) -> ForwardMetadata:
-        raise NotImplementedError("B200AttnBackend.forward_extend is not built yet")
+        """qo start offsets (cumsum of extend_seq_lens) and the longest extend of the batch.
+        extend_seq_lens_cpu / extend_start_loc are filled by ForwardBatch.init_new
+        (forward_batch_info.py:348-369); the fallbacks mirror triton_backend.py:393-431."""
+        ext = forward_batch.extend_seq_lens
+        start = forward_batch.extend_start_loc
+        if start is None:
+            start = torch.zeros_like(ext)
+            start[1:] = torch.cumsum(ext[:-1], dim=0)
+        if forward_batch.extend_seq_lens_cpu is not None:
+            max_len = max(forward_batch.extend_seq_lens_cpu, default=0)
+            total = sum(forward_batch.extend_seq_lens_cpu)
+        else:
+            max_len = int(ext.max().item()) if ext.numel() else 0
+            total = int(ext.sum().item()) if ext.numel() else 0
+        return ForwardMetadata(qo_indptr=start.to(torch.int32), max_extend_len=int(max_len),
+                               total_extend=int(total))
 
     # ------------------------------------------------------------------ CUDA graph hooks
     def init_cuda_graph_state(self, max_bs: int):
@@ -170,7 +185,44 @@ class B200AttnBackend(AttentionBackend):
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
-        raise NotImplementedError("B200AttnBackend.forward_extend is not built yet")
+        hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
+        d, dv = layer.qk_head_dim, layer.v_head_dim
+        q = q.reshape(-1, hq * d)
+        if q.stride(-1) != 1:
+            q = q.contiguous()
+        o = q.new_empty((q.shape[0], hq * dv))
+        pool = forward_batch.token_to_kv_pool
+        if save_kv_cache:
+            # new tokens' K/V go to the pool first; the kernel then gathers prefix AND new keys
+            # from the pool, exactly like the oracle (torch_native_backend.py:196-199)
+            k_cache, v_cache = self._save_kv(layer, forward_batch, k, v)
+        else:
+            k_cache = pool.get_key_buffer(layer.layer_id)
+            v_cache = pool.get_value_buffer(layer.layer_id)
+        md = self.forward_metadata
+        bs = forward_batch.batch_size
+        if q.shape[0] == 0 or bs == 0 or md.max_extend_len == 0:
+            return o
+        if k_cache.dtype != q.dtype:
+            raise _lib.B200Error(
+                f"B200AttnBackend.forward_extend: KV cache dtype {k_cache.dtype} != q dtype "
+                f"{q.dtype} (FP8 KV cache is a later row of the scope table)")
+        attn_type = getattr(layer, "attn_type", None)
+        causal = not (layer.is_cross_attention or
+                      getattr(attn_type, "value", attn_type) == "encoder_only")
+        req_to_token = forward_batch.req_to_token_pool.req_to_token
+        rc = self.lib.b200_attn_extend(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
+            _as_i64(forward_batch.req_pool_indices).data_ptr(),
+            _as_i64(forward_batch.seq_lens).data_ptr(),
+            forward_batch.extend_prefix_lens.to(torch.int32).data_ptr(),
+            forward_batch.extend_seq_lens.to(torch.int32).data_ptr(), md.qo_indptr.data_ptr(), bs,
+            md.max_extend_len, hq, hkv, d, dv, float(layer.scaling),
+            float(layer.logit_cap or 0.0), 1 if causal else 0, _lib.dtype_code(q.dtype),
+            _lib.current_stream())
+        _lib.check(rc, "b200_attn_extend")
+        return o
 
     def support_triton(self):
         return False
