@@ -157,6 +157,29 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
                            int64_t bs_row_stride, const void* bias, void* out, int64_t ldc, int M,
                            int N, int K, int out_dtype, void* stream);
 
+/* ---- INT4 weight-only (W4A16): AWQ / GPTQ ------------------------------------- */
+/* Bit-exact AWQ dequant with the reference layouts (replaces sgl_kernel.awq_dequantize,
+ * sgl-kernel/csrc/gemm/awq_kernel.cu:126-219): qweight [K, N/8] int32, qzeros [K/g, N/8] int32,
+ * scales [K/g, N] f16/bf16 -> out [K, N]; out[k, 8c+j] = (nib(qweight[k,c], ORDER[j]) -
+ * nib(qzeros[k/g,c], ORDER[j])) * scales[k/g, 8c+j], ORDER = [0,4,1,5,2,6,3,7].                 */
+int b200_awq_dequant(const void* qweight, const void* scales, const void* qzeros, void* out, int K,
+                     int N, int group_size, int dtype, void* stream);
+/* One-time repacks used by process_weights_after_loading (awq.py:192, vllm GPTQLinearMethod):
+ *   packed zeros [G, N/8] -> 16-bit zeros [G, N] holding MAGIC + z (+1 for GPTQ v1), MAGIC = 1024
+ *   (f16) / 128 (bf16); awq_order selects the AWQ interleaved or GPTQ sequential nibble order.
+ *   GPTQ qweight [K/8, N] (K-packed) -> [K, N/8] in the AWQ nibble order; perm (nullable, int32 [K])
+ *   gathers source rows (desc_act checkpoints: perm = argsort(g_idx)).                          */
+int b200_w4a16_unpack_zeros(const void* qzeros, void* zeros_out, int num_groups, int N,
+                            int awq_order, int add_one, int dtype, void* stream);
+int b200_w4a16_repack_gptq(const void* qweight, const int32_t* perm, void* out, int K, int N,
+                           void* stream);
+/* Fused dequant + GEMM on tcgen05 (replaces awq_dequantize + torch.matmul, awq.py:203-215, and
+ * vllm ops.gptq_gemm): out[M,N] = x[M,K] @ W[K,N] (+ bias), W[k,n] = round16((w - z) * s) with
+ * qweight [K, N/8] in AWQ order, zeros/scales [K/g, N] as produced above; x/out/bias f16 or bf16. */
+int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void* zeros,
+                    const void* scales, const void* bias, void* out, int64_t ldc, int M, int N,
+                    int K, int group_size, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -49,6 +49,13 @@ _SIGNATURES = {
     "b200_fp8_gemm_block128": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
                                        c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_awq_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                 c_int, c_void_p]),
+    "b200_w4a16_unpack_zeros": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                        c_void_p]),
+    "b200_w4a16_repack_gptq": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "b200_w4a16_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
 }
 
 

@@ -1,0 +1,129 @@
+"""GPU parity of the INT4 weight-only path: bit-exact unpack / dequant / repack and the fused
+tcgen05 W4A16 GEMM behind AWQLinearMethod / GPTQLinearMethod."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import int4 as O
+
+pytestmark = pytest.mark.gpu
+I32_MAX = torch.iinfo(torch.int32).max
+
+
+def _rand_i32(shape, g):
+    # random bit patterns incl. the sign bit (the reference test only draws non-negative words)
+    return torch.from_numpy(np.random.RandomState(int(g)).randint(-2**31, 2**31, size=shape,
+                                                                  dtype=np.int64).astype(np.int32))
+
+
+@pytest.mark.parametrize("rows,cols", [(128, 16), (256, 64), (1024, 128), (3584, 448), (512, 576)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("group", [None, 128])
+def test_awq_dequant_bit_exact(rows, cols, dtype, group):
+    """Shapes / distributions of sgl-kernel/tests/test_awq_dequant.py:67-112 (its tolerance is
+    rtol 1e-3 / atol 1e-5; here the result must be bit-identical to the torch reference)."""
+    from sglang_security_b200.layers.quantization.w4a16_kernel import awq_dequantize
+
+    g = torch.Generator().manual_seed(rows + cols)
+    group_size = group or rows
+    qweight = _rand_i32((rows, cols), rows * 3 + cols)
+    qzeros = _rand_i32((rows // group_size, cols), rows * 5 + cols)
+    scales = torch.rand((rows // group_size, cols * 8), generator=g).to(dtype)
+    ref = O.awq_dequantize_oracle(qweight, scales, qzeros, group_size)
+    out = awq_dequantize(qweight.cuda(), scales.cuda(), qzeros.cuda())
+    assert out.dtype == dtype and out.shape == (rows, cols * 8)
+    assert torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16))
+
+
+def test_gptq_repack_and_zero_unpack_bit_exact():
+    from sglang_security_b200.layers.quantization.w4a16_kernel import repack_gptq, unpack_zeros
+
+    k, n, group = 512, 384, 128
+    qweight = _rand_i32((k // 8, n), 1)
+    qzeros = _rand_i32((k // group, n // 8), 2)
+    ints = O.unpack_gptq_qweight(qweight)                       # [K, N] integers
+    packed = repack_gptq(qweight.cuda()).cpu()                  # [K, N/8] AWQ order
+    assert torch.equal(O.unpack_awq_int4(packed), ints)
+    perm = torch.from_numpy(np.random.RandomState(3).permutation(k))
+    packed_p = repack_gptq(qweight.cuda(), perm.cuda()).cpu()
+    assert torch.equal(O.unpack_awq_int4(packed_p), ints[perm])
+    for dtype, magic in ((torch.float16, 1024), (torch.bfloat16, 128)):
+        z = unpack_zeros(qzeros.cuda(), dtype, awq_order=False, add_one=True).cpu()
+        assert torch.equal(z.float(), (O.unpack_gptq_qzeros(qzeros) + magic).float())
+        z = unpack_zeros(qzeros.cuda(), dtype, awq_order=True, add_one=False).cpu()
+        assert torch.equal(z.float(), (O.unpack_awq_int4(qzeros) + magic).float())
+
+
+def _awq_layer(k, n, group, dtype, seed, realistic=False):
+    g = torch.Generator().manual_seed(seed)
+    if realistic:
+        # asymmetric group quantisation of N(0, 0.02) weights (SURVEY §8d cfg 4 "realistic variant")
+        w = torch.randn((k, n), generator=g) * 0.02
+        wg = w.view(k // group, group, n)
+        lo, hi = wg.amin(1), wg.amax(1)
+        scale = ((hi - lo).clamp(min=1e-5) / 15).to(dtype)
+        zero = (-lo / scale.float()).round().clamp(0, 15).to(torch.int32)
+        q = ((wg / scale.float().unsqueeze(1)).round() + zero.unsqueeze(1)).clamp(0, 15).to(torch.int32).view(k, n)
+        pack = lambda t: sum(((t.view(t.shape[0], -1, 8)[..., j]) & 0xF) << (4 * O.AWQ_ORDER[j])
+                             for j in range(8)).to(torch.int32)
+        return pack(q), scale, pack(zero)
+    return (_rand_i32((k, n // 8), seed), (torch.rand((k // group, n), generator=g) * 0.02).to(dtype),
+            _rand_i32((k // group, n // 8), seed + 1))
+
+
+@pytest.mark.parametrize("m", [1, 16, 130, 1024])
+@pytest.mark.parametrize("k,n,group", [(512, 256, 128), (5120, 3584, 128), (2560, 5120, 128),
+                                       (256, 136, 32), (1024, 1000, 64)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_awq_linear_method(m, k, n, group, dtype):
+    from sglang_security_b200.layers.linear import ColumnParallelLinear
+    from sglang_security_b200.layers.quantization.awq import AWQConfig
+
+    if m * k * n > 2 ** 32:
+        pytest.skip("oracle too slow")
+    qweight, scales, qzeros = _awq_layer(k, n, group, dtype, seed=m + k + n, realistic=(n % 128 == 0))
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn((m, k), generator=g).to(dtype)
+    bias = torch.randn((n,), generator=g).to(dtype)
+    layer = ColumnParallelLinear(k, n, bias=True, params_dtype=dtype,
+                                 quant_config=AWQConfig(4, group, True), tp_rank=0, tp_size=1).cuda()
+    layer.qweight.data.copy_(qweight)
+    layer.qzeros.data.copy_(qzeros)
+    layer.scales.data.copy_(scales)
+    layer.bias.data.copy_(bias)
+    layer.quant_method.process_weights_after_loading(layer)
+    out, _ = layer(x.cuda())
+    ref = O.w4a16_linear_oracle(x, O.awq_dequantize_oracle(qweight, scales, qzeros, group), bias)
+    # reference tolerance for x @ dequant in 16 bit: rtol 1e-2 (SURVEY §8d cfg 4)
+    err = (out.cpu().float() - ref.float()).abs()
+    tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
+    assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
+
+
+@pytest.mark.parametrize("desc_act", [False, True])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_gptq_linear_method(desc_act, dtype):
+    from sglang_security_b200.layers.linear import RowParallelLinear
+    from sglang_security_b200.layers.quantization.gptq import GPTQConfig
+
+    k, n, group, m = 1024, 768, 128, 45
+    g = torch.Generator().manual_seed(11)
+    qweight = _rand_i32((k // 8, n), 21)
+    qzeros = _rand_i32((k // group, n // 8), 22)
+    scales = (torch.rand((k // group, n), generator=g) * 0.02).to(dtype)
+    g_idx = torch.arange(k, dtype=torch.int32) // group
+    if desc_act:
+        g_idx = g_idx[torch.from_numpy(np.random.RandomState(5).permutation(k))]
+    x = torch.randn((m, k), generator=g).to(dtype)
+    layer = RowParallelLinear(k, n, bias=False, params_dtype=dtype,
+                              quant_config=GPTQConfig(4, group, desc_act), tp_rank=0, tp_size=1).cuda()
+    layer.qweight.data.copy_(qweight)
+    layer.qzeros.data.copy_(qzeros)
+    layer.scales.data.copy_(scales)
+    layer.g_idx.data.copy_(g_idx)
+    layer.quant_method.process_weights_after_loading(layer)
+    out, _ = layer(x.cuda())
+    ref = O.w4a16_linear_oracle(x, O.gptq_dequantize_oracle(qweight, scales, qzeros, g_idx, group))
+    err = (out.cpu().float() - ref.float()).abs()
+    tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
+    assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
