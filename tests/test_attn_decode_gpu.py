@@ -38,7 +38,8 @@ def test_decode_matches_oracle_and_golden(name, splits):
 
 
 @pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (8, 1, 128), (40, 8, 128),
-                                      (6, 2, 128), (16, 1, 64), (3, 3, 64)])
+                                      (6, 2, 128), (16, 1, 64), (3, 3, 64), (32, 2, 128),
+                                      (24, 2, 128), (40, 2, 64), (64, 8, 128)])
 def test_decode_geometries(hq, hkv, d):
     case = scenarios.make_attention_case(seed=hq * 100 + d, hq=hq, hkv=hkv, d=d,
                                          seq_lens=[1, 2, 15, 16, 17, 63, 64, 65, 300, 1025])
@@ -50,6 +51,16 @@ def test_decode_long_context_many_splits():
     case = scenarios.make_attention_case(seed=5, hq=32, hkv=8, d=128, seq_lens=[4097, 2500, 8191, 1])
     for splits in (1, 8, 16, 33):
         _check(case, num_kv_splits=splits)
+
+
+def test_decode_vectorised_slot_fetch_paths():
+    """req_to_token row stride % 4 == 0 -> 16-byte slot-id loads for full tiles, scalar loads on
+    the ragged tail; odd strides -> scalar everywhere.  Both must give identical results."""
+    for lens in ([4096, 2500, 1, 48, 96, 97, 49, 47], [4093, 16, 32, 33]):
+        case = scenarios.make_attention_case(seed=9, hq=32, hkv=8, d=128, seq_lens=lens)
+        assert (case.req_to_token.shape[1] % 4 == 0) == (lens[0] == 4096)
+        for splits in (0, 1, 5):
+            _check(case, num_kv_splits=splits)
 
 
 def test_decode_distribution_with_offset():

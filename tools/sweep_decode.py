@@ -72,6 +72,7 @@ def run_point(bs, ctx, hq, hkv, d, layers, slots_mode, splits, iters, ragged=Fal
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--tune", action="store_true", help="cfg-2 point only, a few split counts")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep_decode.json"))
     args = ap.parse_args()
     peak = 6541.5
@@ -84,7 +85,13 @@ def main():
     for slots in ("random", "contiguous"):
         for s in ([0, 1, 4, 8] if args.quick else [0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 16]):
             points.append(dict(bs=64, ctx=4096, hq=32, hkv=8, d=128, layers=4, slots_mode=slots, splits=s))
-    if not args.quick:
+    if args.tune:
+        sm = os.environ.get("SWEEP_SLOTS", "random")
+        points = [dict(bs=64, ctx=4096, hq=32, hkv=8, d=128, layers=4, slots_mode=sm, splits=s)
+                  for s in (0, 2, 3, 4, 5, 6, 8)]
+        points.append(dict(bs=64, ctx=4096, hq=64, hkv=8, d=128, layers=4, slots_mode="random", splits=0))
+        points.append(dict(bs=64, ctx=4096, hq=8, hkv=1, d=128, layers=16, slots_mode="random", splits=0))
+    if not args.quick and not args.tune:
         points += [
             dict(bs=64, ctx=4096, hq=32, hkv=8, d=128, layers=4, slots_mode="random", splits=0, ragged=True),
             dict(bs=1, ctx=4096, hq=32, hkv=8, d=128, layers=8, slots_mode="random", splits=0),
