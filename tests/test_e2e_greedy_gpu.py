@@ -68,5 +68,8 @@ def test_greedy_streams_match_fp8_llama_geometry_small():
     cfg = MS.StackConfig(hidden=1024, heads=8, kv_heads=2, head_dim=128, inter=2816, layers=4,
                          vocab=8192, qkv_bias=False, quant="fp8")
     ref, gpu, tok_ref, tok_gpu, lr, lg = _session(cfg, decode_steps=8, bs=4, prefix=200, own=9)
-    mism, worst = _check_streams(tok_ref, tok_gpu, lr, lg, logit_tol=1.5e-1)
+    # FP8 re-quantisation amplifies bf16-ulp differences between cuBLAS/oneDNN and between the
+    # tcgen05 and CPU accumulation orders: perturbing the ORACLE's own embeddings by 0.2 % (half a
+    # bf16 ulp) moves its logits (std 0.64) by 0.23, the B200 path differs from the oracle by 0.24.
+    mism, worst = _check_streams(tok_ref, tok_gpu, lr, lg, logit_tol=3.5e-1)
     assert mism <= 0.1 * tok_ref.numel(), (mism, worst)
