@@ -124,6 +124,31 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic_per_launch(kernel_substr: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the
+    newest `ncu --set full` capture summarised under profiles/ (tools/ncu_summarize.py); None when
+    no capture of that kernel is committed."""
+    import glob
+    import re
+
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+    def parse(v):
+        m = re.match(r"([0-9.]+)\s*(\w+)", v or "")
+        return float(m.group(1)) * unit.get(m.group(2), float("nan")) if m else float("nan")
+
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_decode_full_summary.json")),
+                       reverse=True):
+        try:
+            recs = [r for r in json.load(open(path)) if kernel_substr in (r.get("Kernel Name") or "")]
+            vals = [parse(r["dram__bytes_read.sum"]) + parse(r["dram__bytes_write.sum"]) for r in recs]
+            if vals:
+                return sum(vals) / len(vals), os.path.relpath(path, ROOT)
+        except Exception:
+            continue
+    return None, None
+
+
 # --------------------------------------------------------------------------------------------
 def cpu_reference_leg(steps: int, warmup: int, layers_total: int, full: bool):
     """Times the reference's CPU decode attention on the host cores on a bounded sample of the
@@ -387,10 +412,13 @@ def run_b200(args):
     t_split = (ms_split / n_split) * 1e-3 if n_split else float("nan")
     achieved = per_launch_bytes / t_split / 1e9 if n_split else None
     layer_bytes = algorithmic_bytes_per_layer(bs, ctx, hq, hkv, d)
-    roofline = {"bound": "hbm", "kernel": "attn_decode_split_kernel", "achieved": achieved,
+    # the committed ncu capture is of the N=1 default workload; other shapes have no traffic figure
+    traffic, traffic_src = ncu_traffic_per_launch("attn_decode_mma_kernel") \
+        if (world == 1 and not args.layers) else (None, None)
+    roofline = {"bound": "hbm", "kernel": "attn_decode_mma_kernel", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                 "frac_of_nominal_8TBs": (achieved / 8000.0) if achieved else None,
-                "peak_source": peak_src, "traffic": None,
+                "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
                 "bytes_per_launch": per_launch_bytes,
                 "us_per_launch": t_split * 1e6 if n_split else None,
                 "launches_timed": n_split,

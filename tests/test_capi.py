@@ -49,7 +49,7 @@ def test_host_side_helpers_need_no_gpu(lib_path):
     s = lib.b200_attn_decode_num_splits(64, 8, 4, 128, 4096, 148)
     assert 1 <= s <= 64
     assert lib.b200_attn_decode_num_splits(1, 8, 4, 128, 100, 148) == 1
-    assert lib.b200_attn_decode_split_align(128, 4) == 64
+    assert lib.b200_attn_decode_split_align(128, 4) == 48  # 3 warps x 16-token tiles
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
