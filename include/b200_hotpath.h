@@ -146,6 +146,13 @@ int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb,
                          void* out, int64_t ldc, int M, int N, int K, int out_dtype,
                          void* stream);
 
+/* M <= max_m (default 128, the decode regime) is served by a dedicated weight-streaming kernel
+ * (swap-AB tcgen05 tiles, thread-block-cluster split-K reduced through distributed shared memory);
+ * this hook lets tests and sweeps force either path: max_m = 0 disables it, splits > 0 fixes the
+ * cluster size, negative values restore the defaults (B200_SMALLM_MAX_M / B200_SMALLM_SPLITS).
+ * Applies to b200_fp8_gemm_rowcol and b200_fp8_gemm_block128.                                   */
+int b200_fp8_gemm_smallm_config(int max_m, int splits);
+
 /* ---- FP8 block-scaled GEMM (128x128 weight blocks, 1x128 activation groups) -------- */
 /* Replaces fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:345-423) and
  * w8a8_block_fp8_matmul (python/sglang/srt/layers/quantization/fp8_kernel.py:774-891):
@@ -179,6 +186,41 @@ int b200_w4a16_repack_gptq(const void* qweight, const int32_t* perm, void* out, 
 int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void* zeros,
                     const void* scales, const void* bias, void* out, int64_t ldc, int M, int N,
                     int K, int group_size, int dtype, void* stream);
+
+/* ---- steps either side of the GEMMs / attention ------------------ */
+/* (residual +) RMSNorm, optionally fused with the FP8 activation quantiser of the linear layer that
+ * consumes it.  Replaces RMSNorm.forward (python/sglang/srt/layers/layernorm.py:61-108; oracle =
+ * forward_native :88-108; GPU = sgl_kernel rmsnorm / fused_add_rmsnorm) followed by
+ * sgl_per_token_quant_fp8 / per_token_group_quant_fp8 (fp8_utils.py:454-648):
+ *   s = x (+ residual) in fp32; residual <- T(s) (in place, if given);
+ *   y = T((s * rsqrt(mean(s^2) + eps)) * weight)
+ *   out (nullable) <- y;  quant_mode 1: scales[m] = absmax(y)/448, q = sat(y * (1/scale));
+ *   quant_mode 2: per 128 columns, scales[m*row_stride + g*col_stride] = max(absmax, quant_eps)/448,
+ *   q = sat(y / scale).  Same bytes as b200_fp8_quant_* applied to `out`.  K %% 8 == 0, K <= 16384. */
+int b200_rmsnorm(const void* x, int64_t ldx, void* residual, int64_t ldr, const void* weight,
+                 void* out, int64_t ldo, void* q, int64_t ldq, float* scales,
+                 int64_t scale_row_stride, int64_t scale_col_stride, int M, int K, float eps,
+                 int quant_mode, float quant_eps, int dtype, void* stream);
+/* SiluAndMul (python/sglang/srt/layers/activation.py:42-51; oracle forward_native :43-45):
+ *   y = T(T(silu(x[:, :d])) * x[:, d:]), x [M, 2d]; out / q / scales / quant_mode as above.     */
+int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* q, int64_t ldq,
+                      float* scales, int64_t scale_row_stride, int64_t scale_col_stride, int M,
+                      int d, int quant_mode, float quant_eps, int dtype, void* stream);
+/* Rotary embedding of q and k IN PLACE, optionally fused with the KV-pool write of (rotated k, v).
+ * Replaces RotaryEmbedding.forward (python/sglang/srt/layers/rotary_embedding.py:119-176; oracle
+ * forward_native + _apply_rotary_emb :30-57; GPU sgl-kernel apply_rope_with_cos_sin_cache_inplace)
+ * and MHATokenToKVPool.set_kv_buffer (memory_pool.py:378-412).
+ *   positions int64 [T]; q [T, Hq*D], k [T, Hkv*D], v [T, Hkv*D] token strides in elements;
+ *   cos_sin_cache [max_pos, rotary_dim] (cos half then sin half), fp32 (B200_F32) or the
+ *   activation dtype; is_neox: pairs (j, j + rotary_dim/2), else adjacent pairs;
+ *   native_rounding != 0 reproduces torch's 16-bit arithmetic of forward_native bit for bit,
+ *   0 computes in fp32 with one rounding (the reference's CUDA kernel);
+ *   k_cache/v_cache (nullable, together): rows loc[t] receive the rotated k and v of token t. */
+int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void* k,
+                       int64_t k_stride, const void* v, int64_t v_stride,
+                       const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
+                       int native_rounding, void* k_cache, void* v_cache, int64_t cache_row_stride,
+                       const int64_t* loc, int T, int Hq, int Hkv, int D, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -89,3 +89,56 @@ def load_test_module(rel_path: str, name: str):
     mod = types.ModuleType(name)
     mod.__file__ = path
     return mod, src
+
+
+_elementwise = None
+
+
+def load_elementwise_layers():
+    """Returns (RMSNorm, SiluAndMul, RotaryEmbedding) classes of the UNMODIFIED reference
+    (layers/layernorm.py, layers/activation.py, layers/rotary_embedding.py + custom_op.py), loaded
+    by file path.  `is_cuda()` is stubbed True (otherwise layernorm.py swaps its own RMSNorm for
+    vllm's at the bottom of the file) with an empty `sgl_kernel` stub for the CUDA-op imports; the
+    callers invoke `forward_native` explicitly — the torch-native implementation the north star
+    names.  With is_cuda True the rotary cos/sin cache stays fp32 (rotary_embedding.py:79-81)."""
+    global _elementwise
+    if _elementwise is not None:
+        return _elementwise
+    if not available():
+        raise RuntimeError(f"reference tree not found under {REF_ROOT}")
+    saved = {k: v for k, v in sys.modules.items() if k == "sglang" or k.startswith("sglang.")}
+    try:
+        for n in ["sglang", "sglang.srt", "sglang.srt.layers", "sglang.srt.layers.quantization"]:
+            _stub(n)
+        utils = _stub("sglang.srt.utils")
+        utils.is_cuda = lambda: True
+        utils.is_hip = lambda: False
+        saved_sgl = sys.modules.get("sgl_kernel")
+        sk = types.ModuleType("sgl_kernel")
+        for fn in ("fused_add_rmsnorm", "gemma_fused_add_rmsnorm", "gemma_rmsnorm", "rmsnorm",
+                   "gelu_and_mul", "gelu_tanh_and_mul", "silu_and_mul",
+                   "apply_rope_with_cos_sin_cache_inplace"):
+            setattr(sk, fn, None)
+        sys.modules["sgl_kernel"] = sk
+        utils.set_weight_attrs = lambda *a, **k: None
+        dist = _stub("sglang.srt.distributed")
+        dist.divide = lambda a, b: a // b
+        dist.get_tensor_model_parallel_rank = lambda: 0
+        dist.get_tensor_model_parallel_world_size = lambda: 1
+        bc = _stub("sglang.srt.layers.quantization.base_config")
+        bc.QuantizationConfig = object
+        _exec("sglang.srt.custom_op", os.path.join(SRT, "custom_op.py"))
+        ln = _exec("sglang.srt.layers.layernorm", os.path.join(SRT, "layers", "layernorm.py"))
+        act = _exec("sglang.srt.layers.activation", os.path.join(SRT, "layers", "activation.py"))
+        rope = _exec("sglang.srt.layers.rotary_embedding",
+                     os.path.join(SRT, "layers", "rotary_embedding.py"))
+    finally:
+        for k in [k for k in sys.modules if k == "sglang" or k.startswith("sglang.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+        if saved_sgl is not None:
+            sys.modules["sgl_kernel"] = saved_sgl
+        else:
+            sys.modules.pop("sgl_kernel", None)
+    _elementwise = (ln.RMSNorm, act.SiluAndMul, rope.RotaryEmbedding)
+    return _elementwise

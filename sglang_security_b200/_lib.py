@@ -46,9 +46,20 @@ _SIGNATURES = {
     "b200_fp8_gemm_rowcol": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int,
                                      c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_int,
                                      c_int, c_int, c_void_p]),
+    "b200_fp8_gemm_smallm_config": (c_int, [c_int, c_int]),
     "b200_fp8_gemm_block128": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
                                        c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_rmsnorm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
+                             c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_float,
+                             c_int, c_float, c_int, c_void_p]),
+    "b200_silu_and_mul": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
+                                  c_void_p, c_int64, c_int64, c_int, c_int, c_int, c_float, c_int,
+                                  c_void_p]),
+    "b200_rope_kv_write": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                   c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                   c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                   c_void_p]),
     "b200_awq_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                  c_int, c_void_p]),
     "b200_w4a16_unpack_zeros": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,

@@ -11,7 +11,7 @@
 //   acc[m, :] += (As[m,kb] * Bs[nb,kb]) * partial[m, :]
 // (BLOCK_N = 128 = one weight scale block, so the combined scale is a per-thread scalar) while
 // the MMA warp already works on the next K blocks.  Same TMA / mbarrier ring as gemm_tc.cuh.
-#include "gemm_tc.cuh"
+#include "fp8_gemm_smallm.cuh"
 
 namespace b200 {
 
@@ -239,6 +239,23 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
                "b200_fp8_gemm_block128: A/B must be 16-byte aligned with lda/ldb %% 16 == 0");
   B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F16,
                "b200_fp8_gemm_block128: out dtype %d", out_dtype);
+  cudaStream_t st0 = static_cast<cudaStream_t>(stream);
+  // (block-scaled: up to 64 tokens; the 128-token promotion loop is slower than the big tile)
+  if (M <= smallm_max_m() && (M <= 64 || smallm_forced())) {  // decode regime: weight streaming, swap-AB + cluster split-K
+    SmallMParams sp = {};
+    sp.out = out;
+    sp.ldc = ldc;
+    sp.as = as;
+    sp.as_row = as_row_stride;
+    sp.as_col = as_col_stride;
+    sp.bs = bs;
+    sp.bs_row = bs_row_stride;
+    sp.bias = bias;
+    sp.M = M;
+    sp.N = N;
+    sp.K = K;
+    return dispatch_smallm<true>(a, lda, b, ldb, sp, out_dtype, st0, "fp8_block_gemm_smallm");
+  }
   BlockGemmParams p;
   p.out = out;
   p.ldc = ldc;

@@ -3,7 +3,9 @@
 // apply_fp8_linear, python/sglang/srt/layers/quantization/fp8_utils.py:636-648):
 //   out[M,N] = (A_e4m3[M,K] . B_e4m3[N,K]^T) * sa[m] * sb[n] (+ bias[n])  -> bf16 / f16
 // plus the TMA-descriptor helper shared by every tcgen05 kernel of the library.
-#include "gemm_tc.cuh"
+#include "fp8_gemm_smallm.cuh"
+
+#include <cstdlib>
 
 namespace b200 {
 
@@ -53,9 +55,66 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t col
   return 0;
 }
 
+// ---- small-M dispatch knobs (env overrides are for sweeps/tests; defaults are the tuned values) --
+static int env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  return v && *v ? std::atoi(v) : dflt;
+}
+static std::atomic<int> g_smallm_max_m{-1};
+static std::atomic<int> g_smallm_splits{-1};
+static std::atomic<bool> g_smallm_forced{false};
+bool smallm_forced() { return g_smallm_forced.load(std::memory_order_relaxed); }
+
+int smallm_force_mt() {
+  static int v = env_int("B200_SMALLM_FORCE_MT", 0);
+  return v;
+}
+
+int smallm_max_m() {
+  int v = g_smallm_max_m.load(std::memory_order_relaxed);
+  if (v < 0) {
+    v = env_int("B200_SMALLM_MAX_M", 128);
+    if (v > 128) v = 128;
+    g_smallm_max_m.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
+// K-split (= cluster size) of the small-M kernel: the smallest power of two that yields at least
+// one CTA per SM (measured on B200: 128..256 CTAs stream fastest, more only adds reduce work), at
+// least 4 K blocks (64 KiB of weights) per CTA, at most 8 (portable cluster size).
+int smallm_pick_splits(int n_tiles, int num_kb) {
+  int forced = g_smallm_splits.load(std::memory_order_relaxed);
+  if (forced < 0) {
+    forced = env_int("B200_SMALLM_SPLITS", 0);
+    g_smallm_splits.store(forced, std::memory_order_relaxed);
+  }
+  int s;
+  if (forced > 0) {
+    s = forced;
+  } else {
+    const int want = ceil_div(device_sm_count(), n_tiles);
+    const int by_k = num_kb / 4 > 0 ? num_kb / 4 : 1;
+    s = 1;
+    while (s < want && s * 2 <= by_k && s < 8) s *= 2;
+  }
+  if (s > 8) s = 8;
+  if (s > num_kb) s = num_kb;
+  if (s < 1) s = 1;
+  return s;
+}
+
 }  // namespace b200
 
 extern "C" {
+
+/* Test/sweep hook: max_m < 0 / splits < 0 re-read the environment defaults. */
+int b200_fp8_gemm_smallm_config(int max_m, int splits) {
+  b200::g_smallm_max_m.store(max_m > 128 ? 128 : max_m, std::memory_order_relaxed);
+  b200::g_smallm_splits.store(splits, std::memory_order_relaxed);
+  b200::g_smallm_forced.store(max_m > 0, std::memory_order_relaxed);
+  return 0;
+}
 
 int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
                          int sa_stride, const float* sb, int sb_stride, const void* bias,
@@ -82,6 +141,24 @@ int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb,
   ep.N = N;
   ep.K = K;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Decode regime: weight streaming, swap-AB + cluster split-K.  Measured crossover against the
+  // big-tile kernel (profiles/r01_gemm_decode.json): always for M <= 64; for 64 < M <= 128 only when
+  // K is long (down_proj) — the per-SM TMA row rate (128 weight rows + MT token rows per K block)
+  // makes MT = 128 cost as much as a full 128x128 tile.
+  if (M <= smallm_max_m() && (M <= 64 || K >= 8192 || smallm_forced())) {
+    SmallMParams sp = {};
+    sp.out = out;
+    sp.ldc = ldc;
+    sp.sa = sa;
+    sp.sa_stride = sa_stride;
+    sp.sb = sb;
+    sp.sb_stride = sb_stride;
+    sp.bias = bias;
+    sp.M = M;
+    sp.N = N;
+    sp.K = K;
+    return dispatch_smallm<false>(a, lda, b, ldb, sp, out_dtype, st, "fp8_gemm_smallm");
+  }
   // Tile choice: 128x256 when there is enough work to fill the SMs with it, else 128x128.
   const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);
   const bool big = tiles256 >= device_sm_count();

@@ -1,0 +1,388 @@
+// Small-M (decode) FP8 W8A8 GEMM for sm_100a: the weight-streaming, HBM-bound regime M <= 128.
+//
+// Replaces the same reference ops as fp8_gemm.cu / fp8_block_gemm.cu (sgl_kernel.fp8_scaled_mm,
+// fp8_gemm_kernel.cu:1071-1146; fp8_blockwise_scaled_mm / w8a8_block_fp8_matmul,
+// fp8_kernel.py:774-891) for the decode batch sizes of BASELINE cfg 3 (M = 1..128).
+//
+// Why a second kernel: with M <= 128 there is exactly one 128-row token tile, so the big-tile
+// kernel launches only N/128 CTAs (32..48 for the attention projections) and most SMs never touch
+// HBM.  Here the problem is transposed ("swap-AB") and split along K:
+//   * UMMA M = 128 WEIGHT rows (A operand, streamed once from HBM by TMA, 16 KiB per K block),
+//     UMMA N = MT tokens (B operand, MT in {16,32,64,128}; rows >= M are TMA zero fill, no traffic),
+//     accumulator in TMEM: lane = output channel, column = token.
+//   * a thread-block CLUSTER of S CTAs shares one 128-channel tile; CTA r streams K blocks
+//     [r*kbs, (r+1)*kbs).  n_tiles * S CTAs with 2 CTAs resident per SM keep every SM's TMA queue
+//     full.  Partials are reduced through distributed shared memory in a FIXED order (rank 0..S-1),
+//     so the result is deterministic and no global workspace or atomics are needed.
+//   * epilogue: TMEM -> registers; token m of the partial is PUSHED (st.shared::cluster) into the
+//     idle pipeline ring of rank m % S, then each rank sums the S slots of its own tokens from local
+//     smem in rank order, applies scales/bias and stores (S == 1: straight from registers).
+//   * block-scaled variant: each 128-wide K block goes to a fresh TMEM buffer and is promoted into
+//     fp32 registers with As[m,kb] * Bs[n/128,kb] (exact fp32 scale semantics of
+//     native_w8a8_block_fp8_matmul, test_block_fp8.py:276-325).
+#pragma once
+
+#include "gemm_tc.cuh"
+
+namespace b200 {
+
+struct SmallMParams {
+  void* out;
+  int64_t ldc;
+  const float* sa;   // per-token scale (rowcol) or null
+  int sa_stride;
+  const float* sb;   // per-channel scale (rowcol) or null
+  int sb_stride;
+  const float* as;   // block: [M, K/128] at as[m*as_row + kb*as_col]
+  int64_t as_row, as_col;
+  const float* bs;   // block: [N/128, K/128] row stride bs_row
+  int64_t bs_row;
+  const void* bias;
+  int M, N, K;
+  int kb_per_split;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n"
+               "barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+
+template <int MT, bool BLK>
+struct SmallMCfg {
+  static constexpr int W_BYTES = 128 * 128;
+  static constexpr int X_BYTES = MT * 128;
+  // Two CTAs per SM (one for the 128-token block-scaled variant whose accumulators need all
+  // registers).  The weight ring is as deep as shared memory allows — the kernel is bound by bytes
+  // in flight (measured: 3/4/5 stages -> 3.2/4.4/5.7 TB/s) — while the activation ring, fed from
+  // L2 and identical for every CTA, is only NX deep and lags the weight ring.
+  static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : 112 * 1024;
+  static constexpr int NX = MT <= 32 ? 3 : 2;
+  static constexpr int NW = (BUDGET - NX * X_BYTES) / W_BYTES;
+  static constexpr int NBUF = BLK ? (MT <= 64 ? 4 : 2) : 1;
+  static constexpr int TCOLS = (NBUF * MT) < 32 ? 32 : NBUF * MT;
+  static constexpr int PART_BYTES = (MT + 8) * 128 * 4;  // S * ceil(M/S) <= M + S - 1 token slots
+  static constexpr int RING_BYTES = NW * W_BYTES + NX * X_BYTES;
+  static constexpr int BAR_BYTES = (2 * NW + 2 * NBUF) * 8 + 16;
+  static constexpr int SMEM_BYTES = RING_BYTES + BAR_BYTES;
+  static_assert(PART_BYTES <= NW * W_BYTES, "partial tile aliases the weight ring");
+  static_assert(NW > NX && NX >= 2, "ring depths");
+};
+
+template <int MT, bool BLK, typename OutT>
+__global__ void __launch_bounds__(192, (BLK && MT == 128) ? 1 : 2)
+fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                       const __grid_constant__ CUtensorMap tmap_x, const SmallMParams p) {
+  using C = SmallMCfg<MT, BLK>;
+  constexpr int NW = C::NW, NX = C::NX, NBUF = C::NBUF;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];  // SWIZZLE_128B tiles need 1024-byte alignment
+  const uint32_t smem_base = smem_u32(smem_raw);
+  const uint32_t ring_x = smem_base + NW * C::W_BYTES;
+  const uint32_t bars = smem_base + C::RING_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (NW + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * NW + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * NW + NBUF + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * NW + 2 * NBUF);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_base));
+  float* part = reinterpret_cast<float*>(smem_raw);  // [S * ceil(M/S)][128], aliases the W ring
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t S = cluster_nctarank();
+  const int n_tile = blockIdx.x / S;
+  const int num_kb = ceil_div(p.K, 128);
+  const int kb0 = min(num_kb, static_cast<int>(rank) * p.kb_per_split);
+  const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+  const int nkb = kb1 - kb0;
+  const bool has_work = nkb > 0;
+
+  // K block i (local index) uses weight slot i % NW and activation slot i % NX; both loads credit
+  // full_bar(i % NW).  The MMA of block i frees both slots with one commit on empty_bar(i % NW).
+  auto issue_w = [&](int i) {
+    const int s = i % NW;
+    tc::mbar_arrive_expect_tx(full_bar(s), C::W_BYTES + C::X_BYTES);
+    const uint32_t sw = smem_base + s * C::W_BYTES;
+    tc::tma_load_2d_hint(sw, &tmap_w, full_bar(s), (kb0 + i) * 128, n_tile * 128, tc::kEvictFirst);
+  };
+  auto issue_x = [&](int i) {
+    tc::tma_load_2d_hint(ring_x + (i % NX) * C::X_BYTES, &tmap_x, full_bar(i % NW),
+                         (kb0 + i) * 128, 0, tc::kEvictLast);
+  };
+  auto wait_mma_done = [&](int i) { tc::mbar_wait(empty_bar(i % NW), (i / NW) & 1u); };
+
+  if (warp == 0 && lane == 0) {
+    if ((smem_base & 1023u) != 0) __trap();
+    tc::prefetch_tmap(&tmap_w);
+    tc::prefetch_tmap(&tmap_x);
+    for (int s = 0; s < NW; ++s) {
+      tc::mbar_init(full_bar(s), 1);
+      tc::mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < NBUF; ++a) {
+      tc::mbar_init(tfull_bar(a), 1);
+      tc::mbar_init(tempty_bar(a), 4);
+    }
+    tc::fence_barrier_init();
+    // Fill both rings BEFORE the CTA-wide setup barrier (TMEM allocation, barrier visibility): the
+    // first weight bytes are in flight while the rest of the CTA is still being set up.
+    for (int i = 0; i < NW && i < nkb; ++i) {
+      issue_w(i);
+      if (i < NX) issue_x(i);
+    }
+  }
+  if (warp == 1) {
+    tc::tmem_alloc(tmem_slot, C::TCOLS);
+    tc::tmem_relinquish();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer: stream this rank's K slice of the weight tile ==========
+    if (lane == 0) {
+      for (int i = NW; i < nkb; ++i) {  // W runs NW blocks ahead of the MMA, X only NX blocks
+        wait_mma_done(i - NW);
+        issue_w(i);
+        issue_x(i - NW + NX);
+      }
+      for (int j = NX + (nkb > NW ? nkb - NW : 0); j < nkb; ++j) {
+        wait_mma_done(j - NX);
+        issue_x(j);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer ==========================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(0, 0, 128, MT, 0, 0);
+      for (int i = 0; i < nkb; ++i) {
+        const int buf = BLK ? i % NBUF : 0;
+        if (BLK) tc::mbar_wait(tempty_bar(buf), ((i / NBUF) & 1u) ^ 1u);
+        tc::mbar_wait(full_bar(i % NW), (i / NW) & 1u);
+        tc::tc_fence_after();
+        const uint32_t sw = smem_base + (i % NW) * C::W_BYTES;
+        const uint32_t sx = ring_x + (i % NX) * C::X_BYTES;
+        const uint32_t tmem_d = tmem_base + buf * MT;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t adesc = tc::make_smem_desc_sw128(sw + k * 32, 1024, 16);
+          const uint64_t bdesc = tc::make_smem_desc_sw128(sx + k * 32, 1024, 16);
+          const uint32_t accum = BLK ? (k != 0) : ((i != 0) | (k != 0));
+          tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, accum ? 1u : 0u);
+        }
+        tc::mma_commit(empty_bar(i % NW));
+        if (BLK) tc::mma_commit(tfull_bar(buf));
+      }
+      if (!BLK && has_work) tc::mma_commit(tfull_bar(0));
+    }
+  } else {
+    // ===================== epilogue ===========================================================
+    // S == 1: TMEM -> registers -> scales/bias -> global (a warp writes 32 consecutive channels).
+    // S  > 1: fixed-order cluster reduction in two phases separated by cluster barriers:
+    //   barrier 1 (after this CTA's last MMA): every peer's pipeline ring is idle and may be
+    //              overwritten;
+    //   push:      token m of my partial goes to rank (m % S), slot [my rank][m / S][channel] of
+    //              ITS ring with st.shared::cluster (fire-and-forget, no round trip);
+    //   barrier 2: all pushes have landed;
+    //   reduce:    each rank sums the S slots of its own tokens from LOCAL smem in rank order
+    //              (deterministic), applies scales/bias and stores.
+    const int quarter = warp & 3;
+    const int ch = quarter * 32 + lane;  // output channel within the tile (TMEM lane)
+    const int n = n_tile * 128 + ch;
+    const bool n_ok = n < p.N;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    OutT* out = static_cast<OutT*>(p.out);
+    float sbn = 1.f, bn = 0.f;
+    if (!BLK && p.sb && n_ok) sbn = __ldg(p.sb + static_cast<int64_t>(n) * p.sb_stride);
+    if (p.bias && n_ok) bn = to_float<OutT>(static_cast<const OutT*>(p.bias)[n]);
+    const int tpr = ceil_div(p.M, static_cast<int>(S));  // tokens per rank (slots per source rank)
+    const uint32_t push_base = smem_base + (rank * tpr * 128 + ch) * 4;
+
+    auto finish = [&](int m, float v) {  // scales + bias + cast + store of one output element
+      float sc = 1.f;
+      if (!BLK) sc = (p.sa ? __ldg(p.sa + static_cast<int64_t>(m) * p.sa_stride) : 1.f) * sbn;
+      if (n_ok) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<OutT>(fmaf(v, sc, bn));
+    };
+    // running (rank, slot) of token m = c*16 + j while the unrolled loops walk m upwards
+    uint32_t dst_rank = 0, dst_slot = 0;
+    auto emit = [&](int m, float v) {
+      if (S == 1) {
+        finish(m, v);
+      } else {
+        const uint32_t a = map_to_rank(push_base + dst_slot * 512, dst_rank);
+        asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(a), "f"(v) : "memory");
+        if (++dst_rank == S) {
+          dst_rank = 0;
+          ++dst_slot;
+        }
+      }
+    };
+
+    if (BLK) {
+      float acc[MT];
+#pragma unroll
+      for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+      const float* bs_row = p.bs + static_cast<int64_t>(n_tile) * p.bs_row;
+      for (int it = 0; it < nkb; ++it) {
+        const int kb = kb0 + it;
+        const int buf = it % NBUF;
+        const float sb = __ldg(bs_row + kb);
+        const float* as_kb = p.as + static_cast<int64_t>(kb) * p.as_col;
+        tc::mbar_wait(tfull_bar(buf), (it / NBUF) & 1u);
+        tc::tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < MT / 16; ++c) {
+          if (c * 16 >= p.M) break;
+          uint32_t r[16];
+          tc::tmem_ld16(lane_addr + buf * MT + c * 16, r);
+          float sc[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int m = c * 16 + j;
+            sc[j] = __ldg(as_kb + static_cast<int64_t>(m < p.M ? m : p.M - 1) * p.as_row) * sb;
+          }
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            acc[c * 16 + j] = fmaf(__uint_as_float(r[j]), sc[j], acc[c * 16 + j]);
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(tempty_bar(buf));
+      }
+      if (S > 1) {
+        __syncwarp();
+        cluster_sync_all();  // barrier 1
+      }
+#pragma unroll
+      for (int m = 0; m < MT; ++m)
+        if (m < p.M) emit(m, acc[m]);
+    } else {
+      if (has_work) {
+        tc::mbar_wait(tfull_bar(0), 0);
+        tc::tc_fence_after();
+      }
+      if (S > 1) {
+        __syncwarp();
+        cluster_sync_all();  // barrier 1
+      }
+#pragma unroll
+      for (int c = 0; c < MT / 16; ++c) {
+        if (c * 16 >= p.M) break;
+        uint32_t r[16];
+        if (has_work) {
+          tc::tmem_ld16(lane_addr + c * 16, r);
+          tc::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) r[j] = 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (c * 16 + j < p.M) emit(c * 16 + j, __uint_as_float(r[j]));
+      }
+    }
+    if (S > 1) {
+      __syncwarp();
+      cluster_sync_all();  // barrier 2: every peer's pushes into my ring are visible
+      const float* mine = part + ch;
+      int m = rank;
+#pragma unroll 4
+      for (int j = 0; j < tpr; ++j, m += S) {
+        if (m >= p.M) break;
+        float sum = 0.f;
+        for (uint32_t q = 0; q < S; ++q) sum += mine[(q * tpr + j) * 128];
+        finish(m, sum);
+      }
+    }
+  }
+  if (warp < 2 && S > 1) {  // producer / MMA warps take part in the two cluster barriers
+    __syncwarp();
+    cluster_sync_all();
+    cluster_sync_all();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc(tmem_base, C::TCOLS);
+}
+
+// Host side --------------------------------------------------------------------------------------
+int smallm_max_m();                       // dispatch threshold (B200_SMALLM_MAX_M, default 128)
+int smallm_pick_splits(int n_tiles, int num_kb);
+int smallm_force_mt();
+bool smallm_forced();                      // threshold set explicitly through the test hook
+
+template <int MT, bool BLK, typename OutT>
+int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallMParams p,
+                  cudaStream_t st, const char* timer_name) {
+  using C = SmallMCfg<MT, BLK>;
+  CUtensorMap tw, tx;
+  int rc = make_tmap_2d(&tw, w, p.N, p.K, ldw, 128, 128, 1, true);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tx, x, p.M, p.K, ldx, MT, 128, 1, false);
+  if (rc) return rc;
+  auto kern = fp8_gemm_smallm_kernel<MT, BLK, OutT>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+    attr_done = true;
+  }
+  const int n_tiles = ceil_div(p.N, 128);
+  const int num_kb = ceil_div(p.K, 128);
+  const int S = smallm_pick_splits(n_tiles, num_kb);
+  p.kb_per_split = ceil_div(num_kb, S);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(n_tiles * S, 1, 1);
+  cfg.blockDim = dim3(192, 1, 1);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = S;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  {
+    ScopedKernelTimer timer(timer_name, st);
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
+  }
+  B200_CHECK_LAUNCH("fp8_gemm_smallm_kernel");
+  return 0;
+}
+
+template <bool BLK>
+int dispatch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, const SmallMParams& p,
+                    int out_dtype, cudaStream_t st, const char* timer_name) {
+#define B200_SMALLM_CASE(MT_)                                                                    \
+  return out_dtype == B200_BF16                                                                  \
+             ? launch_smallm<MT_, BLK, __nv_bfloat16>(x, ldx, w, ldw, p, st, timer_name)         \
+             : launch_smallm<MT_, BLK, __half>(x, ldx, w, ldw, p, st, timer_name)
+  const int mt_floor = smallm_force_mt();  // experiments only (B200_SMALLM_FORCE_MT)
+  if (p.M <= 16 && mt_floor <= 16) { B200_SMALLM_CASE(16); }
+  if (p.M <= 32 && mt_floor <= 32) { B200_SMALLM_CASE(32); }
+  if (p.M <= 64 && mt_floor <= 64) { B200_SMALLM_CASE(64); }
+  B200_SMALLM_CASE(128);
+#undef B200_SMALLM_CASE
+}
+
+}  // namespace b200

@@ -141,3 +141,11 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, weight: torch.Tensor, scales_a:
         _lib.current_stream())
     _lib.check(rc, "b200_fp8_gemm_block128")
     return out
+
+
+def fp8_gemm_smallm_config(max_m: int = -1, splits: int = -1) -> None:
+    """Test/sweep hook for the decode-regime GEMM dispatch (b200_fp8_gemm_smallm_config):
+    max_m = 0 forces the big-tile kernels, splits > 0 fixes the cluster split-K factor, negative
+    values restore the defaults."""
+    _lib.check(_lib.load().b200_fp8_gemm_smallm_config(int(max_m), int(splits)),
+               "b200_fp8_gemm_smallm_config")

@@ -12,6 +12,23 @@ from .fp8_kernel import (fp8_blockwise_scaled_mm, fp8_scaled_mm, per_token_group
                          sglang_per_token_quant_fp8, static_quant_fp8)
 
 
+class QuantizedActivation:
+    """An activation that was quantised by the kernel that produced it (fused RMSNorm->quant,
+    SiLU*mul->quant): `q` e4m3 [M, K], `scale` fp32 [M, 1] (per token) or [M, K/128] (per group),
+    `dtype` = the 16-bit dtype the linear output must have.  Passing it to LinearBase.forward /
+    LinearMethod.apply skips the activation quantiser the reference runs inside apply_fp8_linear
+    (fp8_utils.py:454-648); the bytes are the ones that quantiser would have produced."""
+
+    __slots__ = ("q", "scale", "dtype")
+
+    def __init__(self, q: torch.Tensor, scale: torch.Tensor, dtype: torch.dtype):
+        self.q, self.scale, self.dtype = q, scale, dtype
+
+    @property
+    def shape(self):
+        return self.q.shape
+
+
 def convert_to_channelwise(weight_scale: torch.Tensor, logical_widths: List[int]) -> torch.Tensor:
     """Per-partition (fused qkv / gate_up shard) scales -> one scale per output channel [N, 1]."""
     total = sum(logical_widths)
@@ -28,6 +45,13 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
                      use_per_token_if_dynamic: bool = False) -> torch.Tensor:
     """weight is the [K, N] column-major view of the e4m3 [N, K] weight; weight_scale has one
     entry per output channel (or is a scalar)."""
+    if weight_scale.numel() not in (1, weight.shape[1]):
+        raise ValueError("B200 fp8 linear supports per-channel (or per-tensor) weight scales only")
+    if isinstance(input, QuantizedActivation):
+        if input_scale is not None or input.scale.shape[-1] != 1:
+            raise ValueError("pre-quantised activation must be dynamic per-token for this layer")
+        return fp8_scaled_mm(input.q, weight, input.scale, weight_scale, out_dtype=input.dtype,
+                             bias=bias)
     input_2d = input.reshape(-1, input.shape[-1])
     if input_2d.stride(-1) != 1:
         input_2d = input_2d.contiguous()
@@ -36,8 +60,6 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
         qinput, x_scale = static_quant_fp8(input_2d, input_scale, repeat_scale=False)
     else:
         qinput, x_scale = sglang_per_token_quant_fp8(input_2d)
-    if weight_scale.numel() not in (1, weight.shape[1]):
-        raise ValueError("B200 fp8 linear supports per-channel (or per-tensor) weight scales only")
     output = fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)
     return output.view(*output_shape)
 
@@ -51,6 +73,9 @@ def apply_w8a8_block_fp8_linear(input: torch.Tensor, weight: torch.Tensor, block
     assert input_scale is None
     if list(block_size) != [128, 128]:
         raise ValueError(f"B200 block-fp8 linear supports 128x128 weight blocks, got {block_size}")
+    if isinstance(input, QuantizedActivation):
+        return fp8_blockwise_scaled_mm(input.q, weight, input.scale, weight_scale,
+                                       out_dtype=input.dtype, bias=bias)
     input_2d = input.reshape(-1, input.shape[-1])
     if input_2d.stride(-1) != 1:
         input_2d = input_2d.contiguous()

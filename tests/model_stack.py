@@ -1,12 +1,14 @@
 """Test-only decoder stack (Llama/Qwen2 layer structure, models/llama.py:94-98,180-191,245-267)
 used to check greedy token streams end to end.  Two executions of the SAME weights:
 
-  mode "b200"   : GPU.  Attention through RadixAttention -> B200AttnBackend (C-ABI kernels), linear
-                  layers through sglang_security_b200.layers.linear + the configured quant method.
-                  RMSNorm / RoPE / SiLU / embedding are outside the hot path and use
-                  plain torch ops on the device.
+  mode "b200"   : GPU.  sglang_security_b200.model_executor.decoder_layer.B200DecoderLayer:
+                  attention through RadixAttention -> B200AttnBackend, linear layers through the
+                  configured quant method, RMSNorm / RoPE(+KV write) / SiLU*mul through the fused
+                  C-ABI kernels (`fuse=False` launches every op separately in the reference order).
+                  Embedding lookup and lm_head are plain torch ops on the device.
   mode "oracle" : CPU.  Attention through oracle/attention.py over the oracle pools, linear layers
-                  through torch (or the oracle's quantised-linear restatements).
+                  through torch (or the oracle's quantised-linear restatements), RMSNorm / RoPE /
+                  SiLU*mul through oracle/elementwise.py (the reference's forward_native).
 The host-side bookkeeping (slot allocation, req_to_token writes, ForwardBatch fields) emulates
 ScheduleBatch.prepare_for_extend / prepare_for_decode (schedule_batch.py:1117-1291,1464-1527).
 """
@@ -72,18 +74,18 @@ def rope(positions, q, k, head_dim, theta):
 
 class Stack:
     def __init__(self, cfg: StackConfig, weights, mode: str, pool_size: int, max_reqs: int,
-                 max_ctx: int):
+                 max_ctx: int, fuse: bool = True):
         self.cfg, self.mode = cfg, mode
+        self.max_pos = max_ctx + 8
         self.dev = "cuda" if mode == "b200" else "cpu"
         self.w = weights
         self.next_slot = 1
         self.scaling = cfg.head_dim ** -0.5
         if mode == "b200":
             from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
-            from sglang_security_b200.layers.linear import (MergedColumnParallelLinear,
-                                                            QKVParallelLinear, RowParallelLinear)
-            from sglang_security_b200.layers.radix_attention import RadixAttention
+            from sglang_security_b200.layers.rotary_embedding import RotaryEmbedding
             from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
+            from sglang_security_b200.model_executor.decoder_layer import B200DecoderLayer
 
             self.rtp = ReqToTokenPool(max_reqs, max_ctx, self.dev)
             self.kvp = MHATokenToKVPool(pool_size, 1, torch.bfloat16, cfg.kv_heads, cfg.head_dim,
@@ -94,22 +96,23 @@ class Stack:
                 device=self.dev, req_to_token_pool=self.rtp, token_to_kv_pool=self.kvp,
                 model_config=mc, tp_size=1, server_args=SimpleNamespace()))
             qc = self._quant_config()
-            kw = dict(params_dtype=torch.bfloat16, quant_config=qc, tp_rank=0, tp_size=1)
+            # native_rounding: bit-exact with the oracle's (= forward_native's) 16-bit RoPE arithmetic
+            rope_mod = RotaryEmbedding(cfg.head_dim, cfg.head_dim, self.max_pos, cfg.rope_theta, True,
+                                       torch.bfloat16, native_rounding=True).to(self.dev)
             self.layers = []
             for l, lw in enumerate(weights["layers"]):
-                qkv = QKVParallelLinear(cfg.hidden, cfg.head_dim, cfg.heads, cfg.kv_heads,
-                                        bias=cfg.qkv_bias, **kw).to(self.dev)
-                o = RowParallelLinear(cfg.heads * cfg.head_dim, cfg.hidden, bias=False, **kw).to(self.dev)
-                gu = MergedColumnParallelLinear(cfg.hidden, [cfg.inter, cfg.inter], bias=False, **kw).to(self.dev)
-                dn = RowParallelLinear(cfg.inter, cfg.hidden, bias=False, **kw).to(self.dev)
-                for mod, key in ((qkv, "qkv"), (o, "o"), (gu, "gate_up"), (dn, "down")):
+                L = B200DecoderLayer(cfg.hidden, cfg.heads, cfg.kv_heads, cfg.head_dim, cfg.inter, l,
+                                     rope_mod, quant_config=qc, params_dtype=torch.bfloat16,
+                                     rms_norm_eps=cfg.eps, qkv_bias=cfg.qkv_bias, fuse=fuse,
+                                     tp_rank=0, tp_size=1).to(self.dev)
+                for mod, key in ((L.qkv_proj, "qkv"), (L.o_proj, "o"), (L.gate_up_proj, "gate_up"),
+                                 (L.down_proj, "down")):
                     self._load(mod, lw[key])
                 if cfg.qkv_bias:
-                    qkv.bias.data.copy_(lw["qkv_bias"])
-                attn = RadixAttention(cfg.heads, cfg.head_dim, self.scaling, cfg.kv_heads, l)
-                self.layers.append(SimpleNamespace(
-                    qkv=qkv, o=o, gate_up=gu, down=dn, attn=attn,
-                    in_norm=lw["in_norm"].to(self.dev), post_norm=lw["post_norm"].to(self.dev)))
+                    L.qkv_proj.bias.data.copy_(lw["qkv_bias"])
+                L.input_layernorm.weight.data = lw["in_norm"].to(self.dev)
+                L.post_attention_layernorm.weight.data = lw["post_norm"].to(self.dev)
+                self.layers.append(L)
             self.embed = weights["embed"].to(self.dev)
             self.lm_head = weights["lm_head"].to(self.dev)
             self.final_norm = weights["final_norm"].to(self.dev)
@@ -177,33 +180,32 @@ class Stack:
             self.backend.init_forward_metadata(fb)
             h = self.embed[input_ids.to(dev)]
             pos = positions.to(dev)
+            residual = None
             for L in self.layers:
-                x = rmsnorm(h, L.in_norm, cfg.eps)
-                qkv, _ = L.qkv(x)
-                q, k, v = qkv.split([cfg.heads * cfg.head_dim, cfg.kv_heads * cfg.head_dim,
-                                     cfg.kv_heads * cfg.head_dim], dim=-1)
-                q, k = rope(pos, q, k, cfg.head_dim, cfg.rope_theta)
-                a = L.attn(q, k, v, fb)
-                o, _ = L.o(a)
-                h = h + o
-                x = rmsnorm(h, L.post_norm, cfg.eps)
-                gu, _ = L.gate_up(x)
-                y, _ = L.down(F.silu(gu[:, :cfg.inter]) * gu[:, cfg.inter:])
-                h = h + y
-            h = rmsnorm(h[last_idx.to(dev)], self.final_norm, cfg.eps)
+                h, residual = L(pos, h, fb, residual)
+            h = rmsnorm((h + residual)[last_idx.to(dev)], self.final_norm, cfg.eps)
             return F.linear(h, self.lm_head).float().cpu()
         # ---- oracle (CPU)
         from oracle import attention as OA
+        from oracle import elementwise as OE
 
         w = self.w
         h = w["embed"][input_ids]
+        if not hasattr(self, "_cos_sin"):
+            self._cos_sin = OE.cos_sin_cache_oracle(cfg.head_dim, self.max_pos, cfg.rope_theta)
         layer_ns = SimpleNamespace(layer_id=0)
+        residual = None
         for l, lw in enumerate(w["layers"]):
-            x = rmsnorm(h, lw["in_norm"], cfg.eps)
+            # LlamaDecoderLayer.forward (models/llama.py:245-267) over the forward_native ops
+            if residual is None:
+                residual, x = h, OE.rmsnorm_oracle(h, lw["in_norm"], cfg.eps)
+            else:
+                x, residual = OE.rmsnorm_oracle(h, lw["in_norm"], cfg.eps, residual)
             qkv = self._oracle_linear(f"qkv{l}", x, lw["qkv"], lw["qkv_bias"])
             q, k, v = qkv.split([cfg.heads * cfg.head_dim, cfg.kv_heads * cfg.head_dim,
                                  cfg.kv_heads * cfg.head_dim], dim=-1)
-            q, k = rope(positions, q, k, cfg.head_dim, cfg.rope_theta)
+            q, k = OE.rope_oracle(positions, q.contiguous(), k.contiguous(), self._cos_sin,
+                                  cfg.head_dim, cfg.head_dim, True)
             layer_ns.layer_id = l
             self.kvp.set_kv_buffer(layer_ns, fb_fields["out_cache_loc"],
                                    k.reshape(-1, cfg.kv_heads, cfg.head_dim).contiguous(),
@@ -218,12 +220,11 @@ class Stack:
                                                self.rtp.req_to_token, fb_fields["req_pool_indices"],
                                                fb_fields["seq_lens"], fb_fields["prefix_lens"], ext,
                                                self.scaling)
-            h = h + self._oracle_linear(f"o{l}", a.reshape(a.shape[0], -1), lw["o"])
-            x = rmsnorm(h, lw["post_norm"], cfg.eps)
+            o = self._oracle_linear(f"o{l}", a.reshape(a.shape[0], -1), lw["o"])
+            x, residual = OE.rmsnorm_oracle(o, lw["post_norm"], cfg.eps, residual)
             gu = self._oracle_linear(f"gu{l}", x, lw["gate_up"])
-            h = h + self._oracle_linear(f"dn{l}", F.silu(gu[:, :cfg.inter]) * gu[:, cfg.inter:],
-                                        lw["down"])
-        h = rmsnorm(h[last_idx], w["final_norm"], cfg.eps)
+            h = self._oracle_linear(f"dn{l}", OE.silu_and_mul_oracle(gu), lw["down"])
+        h = rmsnorm((h + residual)[last_idx], w["final_norm"], cfg.eps)
         return F.linear(h, w["lm_head"]).float()
 
 

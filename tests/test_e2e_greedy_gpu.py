@@ -76,3 +76,27 @@ def test_greedy_streams_match_fp8_llama_geometry_small():
     # a tie inside the measured noise.  Measured on B200: 8 flips of 36 tokens; cap at one third.
     mism, worst = _check_streams(tok_ref, tok_gpu, lr, lg, logit_tol=3.5e-1)
     assert mism <= tok_ref.numel() // 3, (mism, worst)
+
+
+@pytest.mark.parametrize("quant", [None, "fp8"])
+def test_fused_layer_equals_unfused_layer_bit_exact(quant):
+    """B200DecoderLayer(fuse=True) — RMSNorm->quant, RoPE->KV write, SiLU*mul->quant fused — must
+    give exactly the logits and KV pool of the op-by-op layer in the reference's call order."""
+    cfg = MS.StackConfig(hidden=1024, heads=8, kv_heads=2, head_dim=128, inter=2816, layers=3,
+                         vocab=4096, qkv_bias=quant is None, quant=quant)
+    weights = MS.init_weights(cfg, seed=3, std=0.02)
+    g = torch.Generator().manual_seed(5)
+    prefix_ids = torch.randint(0, cfg.vocab, (70,), generator=g)
+    suffix = [torch.randint(0, cfg.vocab, (n,), generator=g) for n in (5, 9, 1)]
+    kw = dict(pool_size=200, max_reqs=5, max_ctx=100)
+    outs = []
+    for fuse in (True, False):
+        st = MS.Stack(cfg, weights, "b200", fuse=fuse, **kw)
+        tok, logits = MS.run_shared_prefix_session(st, prefix_ids, suffix, 4)
+        outs.append((tok, logits, st))
+    assert torch.equal(outs[0][0], outs[1][0])
+    for a, b in zip(outs[0][1], outs[1][1]):
+        assert torch.equal(a, b)
+    for l in range(cfg.layers):
+        assert torch.equal(outs[0][2].kvp.k_buffer[l], outs[1][2].kvp.k_buffer[l])
+        assert torch.equal(outs[0][2].kvp.v_buffer[l], outs[1][2].kvp.v_buffer[l])

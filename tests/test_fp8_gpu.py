@@ -197,3 +197,67 @@ def test_fp8_linear_method_serialized_checkpoint_static_and_block():
     ref = O.block_fp8_linear_oracle(x, w, b_s)
     rel = (out.cpu().float() - ref.float()).abs().mean() / ref.float().abs().mean()
     assert rel.item() < 1e-3, rel.item()
+
+
+@pytest.fixture
+def smallm_cfg():
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_gemm_smallm_config
+
+    yield fp8_gemm_smallm_config
+    fp8_gemm_smallm_config(-1, -1)
+
+
+@pytest.mark.parametrize("m", [1, 3, 16, 17, 33, 64, 100, 128])
+@pytest.mark.parametrize("n,k,splits", [(4096, 4096, 0), (6144, 4096, 3), (1000, 2048, 8),
+                                        (256, 14336, 5), (4096, 1152, 8), (128, 128, 2)])
+def test_fp8_smallm_cluster_splitk_matches_oracle_and_big_tile_path(m, n, k, splits, smallm_cfg):
+    """Decode-regime kernel (swap-AB, cluster split-K over DSMEM) against the oracle and against
+    the big-tile kernel on identical inputs; forced cluster sizes incl. ragged K splits (empty
+    ranks), N % 128 != 0, M % 16 != 0; two runs must be bit-identical (fixed reduction order)."""
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_scaled_mm
+
+    g = torch.Generator().manual_seed(m * 131 + n + k + splits)
+    a, b = _rand_fp8((m, k), g), _rand_fp8((n, k), g)
+    sa = torch.randn((m,), generator=g) * 0.001
+    sb = torch.randn((n,), generator=g) * 0.001
+    bias = torch.randn((n,), generator=g).to(torch.bfloat16)
+    ref = O.scaled_mm_oracle(a, b.t(), sa, sb, torch.bfloat16, bias)
+    args = (a.cuda(), b.cuda().t(), sa.cuda(), sb.cuda(), torch.bfloat16, bias.cuda())
+    smallm_cfg(128, splits)
+    out = fp8_scaled_mm(*args)
+    out_again = fp8_scaled_mm(*args)
+    smallm_cfg(0, -1)
+    out_big = fp8_scaled_mm(*args)
+    assert torch.equal(out, out_again)
+    torch.testing.assert_close(out.cpu(), ref, rtol=0.02, atol=1)
+    scale = max(1.0, ref.float().abs().max().item())
+    assert (out.cpu().float() - ref.float()).abs().max().item() <= 2e-2 * scale
+    # same fp8 products, fp32 accumulation in a different order: at most one bf16 ulp apart
+    assert (out.float() - out_big.float()).abs().max().item() <= 2 ** -7 * scale
+
+
+@pytest.mark.parametrize("m", [1, 16, 31, 64, 83, 128])
+@pytest.mark.parametrize("n,k,splits", [(512, 7168, 0), (7168, 1024, 0), (1536, 2048, 8),
+                                        (2112, 1152, 4), (128, 128, 1)])
+def test_fp8_block_scaled_smallm(m, n, k, splits, smallm_cfg):
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_blockwise_scaled_mm
+
+    g = torch.Generator().manual_seed(m + n + k + splits)
+    a, b = _rand_fp8((m, k), g), _rand_fp8((n, k), g)
+    a_s = torch.rand((m, (k + 127) // 128), generator=g) * 1e-2
+    b_s = torch.rand(((n + 127) // 128, (k + 127) // 128), generator=g) * 1e-2
+    ref = O.block_scaled_mm_oracle(a, b, a_s, b_s, (128, 128), torch.bfloat16)
+    args = (a.cuda(), b.cuda(), a_s.cuda(), b_s.cuda(), torch.bfloat16)
+    smallm_cfg(128, splits)
+    out = fp8_blockwise_scaled_mm(*args)
+    assert torch.equal(out, fp8_blockwise_scaled_mm(*args))
+    smallm_cfg(0, -1)
+    out_big = fp8_blockwise_scaled_mm(*args)
+    rel = (out.cpu().float() - ref.float()).abs().mean() / ref.float().abs().mean()
+    assert rel.item() < 1e-3, rel.item()
+    rel2 = (out.float() - out_big.float()).abs().mean() / out_big.float().abs().mean()
+    assert rel2.item() < 1e-3, rel2.item()
+    a_s_col = a_s.cuda().t().contiguous().t()  # column-major activation scales
+    smallm_cfg(128, splits)
+    assert torch.equal(out, fp8_blockwise_scaled_mm(a.cuda(), b.cuda(), a_s_col, b_s.cuda(),
+                                                    torch.bfloat16))

@@ -15,6 +15,7 @@ import torch
 
 from sglang_security_b200 import _lib
 from sglang_security_b200.layers.quantization.fp8_kernel import (fp8_blockwise_scaled_mm,
+                                                                fp8_gemm_smallm_config,
                                                                 fp8_scaled_mm)
 
 FP8 = torch.float8_e4m3fn
@@ -36,6 +37,8 @@ def time_events(fn, iters, flush):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ms", default="1,16,64,256,1024,4096,8192,16384")
+    ap.add_argument("--smallm-sweep", action="store_true",
+                    help="for M <= 128 also time the big-tile kernel and forced cluster split-K factors")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bench_gemm.json"))
     args = ap.parse_args()
     dev = "cuda"
@@ -80,6 +83,19 @@ def main():
                     res[name + "_gbs"] = round(bytes_ / t / 1e9, 1)
                 except Exception as e:
                     res[name + "_err"] = str(e)[:80]
+            if args.smallm_sweep and m <= 128:
+                variants = [("big", 0, -1)] + [(f"s{sp}", 128, sp) for sp in (1, 2, 3, 4, 6, 8)]
+                for tag, max_m, sp in variants:
+                    fp8_gemm_smallm_config(max_m, sp)
+                    for name, fn in (
+                        ("rowcol", lambda: fp8_scaled_mm(x, w.t(), sa, sb, torch.bfloat16)),
+                        ("block128", lambda: fp8_blockwise_scaled_mm(x, w, a_s, bs, torch.bfloat16)),
+                    ):
+                        for _ in range(2):
+                            fn()
+                        t = time_events(fn, 7, flush)
+                        res[f"{name}_{tag}_us"] = round(t * 1e6, 1)
+                fp8_gemm_smallm_config(-1, -1)
             print(json.dumps(res), flush=True)
             rows.append(res)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
