@@ -39,6 +39,13 @@ const char* b200_last_error(void);
  * (bench.py's gpu_launches counter). */
 int64_t b200_launch_count(void);
 
+/* Programmatic dependent launch (default on; env B200_PDL=0 turns it off): every kernel of the
+ * library is launched with cudaLaunchAttributeProgrammaticStreamSerialization and orders its own
+ * dependent accesses with griddepcontrol.wait, so consecutive kernels of a decode step overlap
+ * launch latency, prologue and weight prefetch with the tail of their predecessor (also inside a
+ * captured CUDA graph).  Returns the previous setting. */
+int b200_set_pdl(int on);
+
 /* Per-kernel device timing for bench.py's roofline leg: while enabled, the dominant kernels are
  * bracketed by CUDA events on the launching stream (not during graph capture).
  * b200_timing_read sums and clears the records of kernel `name` (NULL/"" = all). Names:

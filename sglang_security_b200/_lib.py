@@ -20,6 +20,7 @@ _SIGNATURES = {
     "b200_version": (c_int, []),
     "b200_last_error": (c_char_p, []),
     "b200_launch_count": (c_int64, []),
+    "b200_set_pdl": (c_int, [c_int]),
     "b200_timing_enable": (c_int, [c_int]),
     "b200_timing_read": (c_int, [c_char_p, ctypes.POINTER(c_int64), ctypes.POINTER(ctypes.c_double)]),
     "b200_kv_write": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
@@ -104,6 +105,12 @@ def check(status: int, what: str) -> None:
     if status != 0:
         msg = load().b200_last_error()
         raise B200Error(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def set_pdl(on) -> int:
+    """Programmatic dependent launch: False/0 off, True/1 on for every kernel, other ints = bit mask
+    over kernel families (experiments).  Returns the previous mask."""
+    return int(load().b200_set_pdl(int(on)))
 
 
 def timing_enable(on: bool) -> None:

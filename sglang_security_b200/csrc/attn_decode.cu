@@ -20,6 +20,8 @@
 //   accumulators and fp32 online softmax in registers (exp2 domain, scale*log2e folded in).
 //   Warps are merged once through shared memory; partials (normalised O, log2-domain LSE) go to
 //   the workspace and are merged by attn_merge_kernel.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -42,6 +44,7 @@ struct DecodeParams {
   int num_splits;
   float qk_scale;   // scale*log2e, or plain scale when logit_cap > 0
   float logit_cap;  // <= 0: disabled
+  int pdl_late;
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -144,6 +147,8 @@ attn_decode_mma_kernel(const DecodeParams p) {
   constexpr int GT = HI ? 16 : 8;
 
   extern __shared__ __align__(128) uint8_t smem[];
+  griddep_wait();  // q, the new KV rows and seq_lens are written by the kernels before this one
+  if (!p.pdl_late) griddep_launch_dependents();
 
   const int split = blockIdx.x;
   const int kvh = blockIdx.y / p.head_tiles;
@@ -347,6 +352,7 @@ attn_decode_mma_kernel(const DecodeParams p) {
     __syncwarp();  // stage may be refilled by the next iteration's issue
   }
   cp_async_wait<0>();
+  if (p.pdl_late) griddep_launch_dependents();
 
   // ---- quad-reduce the row sums, merge warps through shared memory ---------------------------
   l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 1);
@@ -410,6 +416,8 @@ __global__ void attn_merge_kernel(const float* __restrict__ part_o,
                                   const float* __restrict__ part_lse, T* __restrict__ o,
                                   int64_t o_stride, const int64_t* __restrict__ seq_lens, int Hq,
                                   int Dv, int num_splits, int align) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int hq = blockIdx.x, b = blockIdx.y;
   const int len = static_cast<int>(seq_lens[b]);
   if (len <= 0) return;
@@ -458,7 +466,7 @@ static int launch_decode(const DecodeParams& p, cudaStream_t st) {
   dim3 grid(p.num_splits, p.Hkv * p.head_tiles, p.bs);
   {
     ScopedKernelTimer timer("attn_decode_split", st);
-    kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(p);
+    B200_CUDA_OK(launch_kernel(kern, grid, dim3(C::THREADS), C::SMEM_BYTES, st, 1, pdl_family(p.bs, kPdlAttn), p));
   }
   B200_CHECK_LAUNCH("attn_decode_mma_kernel");
   return 0;
@@ -558,6 +566,7 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
   p.num_splits = num_splits;
   p.logit_cap = logit_cap;
   p.qk_scale = logit_cap > 0.f ? scale : scale * kLog2e;
+  { static const char* e = std::getenv("B200_PDL_LATE"); p.pdl_late = e ? std::atoi(e) : 1; }
   p.part_o = static_cast<float*>(workspace);
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
 
@@ -592,13 +601,13 @@ int b200_attn_merge(const float* part_o, const float* part_lse, void* o, int64_t
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   ScopedKernelTimer timer("attn_merge", st);
   if (dtype == B200_BF16)
-    attn_merge_kernel<__nv_bfloat16><<<grid, threads, 0, st>>>(
-        part_o, part_lse, static_cast<__nv_bfloat16*>(o), o_stride, seq_lens, Hq, Dv, num_splits,
-        align);
+    B200_CUDA_OK(launch_kernel(attn_merge_kernel<__nv_bfloat16>, grid, dim3(threads), 0, st, 1, pdl_family(bs, kPdlMerge),
+                               part_o, part_lse, static_cast<__nv_bfloat16*>(o), o_stride, seq_lens,
+                               Hq, Dv, num_splits, align));
   else
-    attn_merge_kernel<__half><<<grid, threads, 0, st>>>(part_o, part_lse, static_cast<__half*>(o),
-                                                        o_stride, seq_lens, Hq, Dv, num_splits,
-                                                        align);
+    B200_CUDA_OK(launch_kernel(attn_merge_kernel<__half>, grid, dim3(threads), 0, st, 1, pdl_family(bs, kPdlMerge), part_o,
+                               part_lse, static_cast<__half*>(o), o_stride, seq_lens, Hq, Dv,
+                               num_splits, align));
   B200_CHECK_LAUNCH("attn_merge_kernel");
   return 0;
 }

@@ -60,11 +60,66 @@ struct ScopedKernelTimer {
   cudaEvent_t start_ = nullptr;
 };
 
+// ---- launches ------------------------------------------------------------------------------
+// Every kernel of the library is launched through launch_kernel(): when programmatic dependent
+// launch is on (b200_set_pdl / B200_PDL, default on) the launch carries
+// cudaLaunchAttributeProgrammaticStreamSerialization, so inside a stream or a captured CUDA graph
+// the NEXT kernel's CTAs may start (and run their prologue: barrier init, TMEM allocation, weight
+// prefetch) while this kernel drains.  Device side, a kernel must call griddep_wait() before it
+// reads anything an earlier kernel wrote or writes anything an earlier kernel may still read, and
+// calls griddep_launch_dependents() once its own dependent-data accesses may begin.
+extern std::atomic<int> g_pdl_on;  // bit mask over PdlFamily (all bits = every kernel)
+enum PdlFamily { kPdlGemmSmall = 1, kPdlGemmBig = 2, kPdlAttn = 4, kPdlMerge = 8, kPdlRow = 16,
+                 kPdlRope = 32, kPdlQuant = 64, kPdlOther = 128 };
+
+// Measured on the Llama-3.1-8B FP8 decode step (profiles/r01_pdl_sweep.md): overlapping launches
+// pays while the step is latency-bound (-7..-10 % at batch <= 32) and costs 3-6 % at batch 64+, where
+// early-resident dependents only take SM resources from a bandwidth-bound predecessor.  Call sites
+// therefore pass pdl_family(tokens, family): the family bit for small token counts, 0 otherwise.
+int pdl_max_tokens();
+inline int pdl_family(int tokens, int family) { return tokens <= pdl_max_tokens() ? family : 0; }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t st, unsigned cluster_x, int family,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (g_pdl_on.load(std::memory_order_relaxed) & family) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 int device_sm_count();
 
 // ---- device helpers -----------------------------------------------------------------------
 __host__ __device__ constexpr int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Programmatic dependent launch (no-ops when the kernel was launched without the attribute).
+__device__ __forceinline__ void griddep_wait() {
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+}
+__device__ __forceinline__ void griddep_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

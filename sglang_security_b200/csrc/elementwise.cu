@@ -177,6 +177,8 @@ __global__ void __launch_bounds__(kRowThreads)
 rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, int64_t ldr,
                const T* __restrict__ weight, int K, float eps, RowOut o) {
   __shared__ float red[32];
+  griddep_wait();
+  griddep_launch_dependents();
   const int m = blockIdx.x;
   const int nvec = K / 8;
   const T* xrow = x + m * ldx;
@@ -220,6 +222,8 @@ template <typename T>
 __global__ void __launch_bounds__(kRowThreads)
 silu_mul_kernel(const T* __restrict__ x, int64_t ldx, int d, RowOut o) {
   __shared__ float red[32];
+  griddep_wait();
+  griddep_launch_dependents();
   const int m = blockIdx.x;
   const int nvec = d / 8;
   const T* grow = x + m * ldx;
@@ -305,6 +309,8 @@ __device__ __forceinline__ void rotate(float x1, float x2, float c, float s, boo
 template <typename T>
 __global__ void __launch_bounds__(256)
 rope_kv_write_kernel(const RopeParams p) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int t = blockIdx.x;
   const int64_t pos = p.positions[t];
   const int cpd = p.D / 8;                                 // chunks per head row
@@ -407,13 +413,14 @@ int b200_rmsnorm(const void* x, int64_t ldx, void* residual, int64_t ldr, const 
   {
     ScopedKernelTimer timer("rmsnorm", st);
     if (dtype == B200_BF16)
-      rmsnorm_kernel<__nv_bfloat16><<<M, kRowThreads, 0, st>>>(
-          static_cast<const __nv_bfloat16*>(x), ldx, static_cast<__nv_bfloat16*>(residual), ldr,
-          static_cast<const __nv_bfloat16*>(weight), K, eps, o);
+      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__nv_bfloat16>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
+                                 static_cast<const __nv_bfloat16*>(x), ldx,
+                                 static_cast<__nv_bfloat16*>(residual), ldr,
+                                 static_cast<const __nv_bfloat16*>(weight), K, eps, o));
     else
-      rmsnorm_kernel<__half><<<M, kRowThreads, 0, st>>>(
-          static_cast<const __half*>(x), ldx, static_cast<__half*>(residual), ldr,
-          static_cast<const __half*>(weight), K, eps, o);
+      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__half>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
+                                 static_cast<const __half*>(x), ldx, static_cast<__half*>(residual),
+                                 ldr, static_cast<const __half*>(weight), K, eps, o));
   }
   B200_CHECK_LAUNCH("rmsnorm_kernel");
   return 0;
@@ -441,10 +448,11 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
   {
     ScopedKernelTimer timer("silu_and_mul", st);
     if (dtype == B200_BF16)
-      silu_mul_kernel<__nv_bfloat16><<<M, kRowThreads, 0, st>>>(
-          static_cast<const __nv_bfloat16*>(x), ldx, d, o);
+      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__nv_bfloat16>, dim3(M), dim3(kRowThreads), 0, st,
+                                 1, pdl_family(M, kPdlRow), static_cast<const __nv_bfloat16*>(x), ldx, d, o));
     else
-      silu_mul_kernel<__half><<<M, kRowThreads, 0, st>>>(static_cast<const __half*>(x), ldx, d, o);
+      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__half>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
+                                 static_cast<const __half*>(x), ldx, d, o));
   }
   B200_CHECK_LAUNCH("silu_mul_kernel");
   return 0;
@@ -478,9 +486,9 @@ int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void
   {
     ScopedKernelTimer timer("rope_kv_write", st);
     if (dtype == B200_BF16)
-      rope_kv_write_kernel<__nv_bfloat16><<<T, 256, 0, st>>>(p);
+      B200_CUDA_OK(launch_kernel(rope_kv_write_kernel<__nv_bfloat16>, dim3(T), dim3(256), 0, st, 1, pdl_family(T, kPdlRope), p));
     else
-      rope_kv_write_kernel<__half><<<T, 256, 0, st>>>(p);
+      B200_CUDA_OK(launch_kernel(rope_kv_write_kernel<__half>, dim3(T), dim3(256), 0, st, 1, pdl_family(T, kPdlRope), p));
   }
   B200_CHECK_LAUNCH("rope_kv_write_kernel");
   return 0;

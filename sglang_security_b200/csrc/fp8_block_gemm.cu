@@ -73,6 +73,8 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  griddep_wait();  // activations / scales come from the previous kernel
+  griddep_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -217,7 +219,7 @@ static int launch_block_gemm(const void* a, int64_t lda, const void* b, int64_t 
   const int sms = device_sm_count();
   {
     ScopedKernelTimer timer("fp8_block_gemm", st);
-    kern<<<tiles < sms ? tiles : sms, 192, SMEM, st>>>(ta, tb, p);
+    B200_CUDA_OK(launch_kernel(kern, dim3(tiles < sms ? tiles : sms), dim3(192), SMEM, st, 1, pdl_family(p.M, kPdlGemmBig), ta, tb, p));
   }
   B200_CHECK_LAUNCH("fp8_block_gemm_kernel");
   return 0;

@@ -65,6 +65,11 @@ static std::atomic<int> g_smallm_splits{-1};
 static std::atomic<bool> g_smallm_forced{false};
 bool smallm_forced() { return g_smallm_forced.load(std::memory_order_relaxed); }
 
+int pdl_late() {
+  static int v = env_int("B200_PDL_LATE", 1);
+  return v;
+}
+
 int smallm_force_mt() {
   static int v = env_int("B200_SMALLM_FORCE_MT", 0);
   return v;

@@ -40,6 +40,7 @@ struct SmallMParams {
   const void* bias;
   int M, N, K;
   int kb_per_split;
+  int pdl_late;  // trigger dependents after the main loop instead of right after the dependency wait
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -140,12 +141,14 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
       tc::mbar_init(tempty_bar(a), 4);
     }
     tc::fence_barrier_init();
-    // Fill both rings BEFORE the CTA-wide setup barrier (TMEM allocation, barrier visibility): the
-    // first weight bytes are in flight while the rest of the CTA is still being set up.
-    for (int i = 0; i < NW && i < nkb; ++i) {
-      issue_w(i);
-      if (i < NX) issue_x(i);
-    }
+    // Fill the weight ring BEFORE the CTA-wide setup barrier AND before the programmatic-launch
+    // dependency wait: weights are never written during a step, so their first NW x 16 KiB are in
+    // flight while the previous kernel of the stream / graph is still draining and the rest of
+    // this CTA is being set up.  Activations (written by the previous kernel) only after the wait.
+    for (int i = 0; i < NW && i < nkb; ++i) issue_w(i);
+    griddep_wait();
+    if (!p.pdl_late) griddep_launch_dependents();
+    for (int i = 0; i < NX && i < nkb; ++i) issue_x(i);
   }
   if (warp == 1) {
     tc::tmem_alloc(tmem_slot, C::TCOLS);
@@ -168,6 +171,7 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
         wait_mma_done(j - NX);
         issue_x(j);
       }
+      if (p.pdl_late) griddep_launch_dependents();  // every load of this CTA has been issued
     }
   } else if (warp == 1) {
     // ===================== MMA issuer ==========================================================
@@ -204,6 +208,7 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
     //   barrier 2: all pushes have landed;
     //   reduce:    each rank sums the S slots of its own tokens from LOCAL smem in rank order
     //              (deterministic), applies scales/bias and stores.
+    griddep_wait();  // scales / bias / output buffers may belong to the previous kernel
     const int quarter = warp & 3;
     const int ch = quarter * 32 + lane;  // output channel within the tile (TMEM lane)
     const int n = n_tile * 128 + ch;
@@ -328,6 +333,7 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
 int smallm_max_m();                       // dispatch threshold (B200_SMALLM_MAX_M, default 128)
 int smallm_pick_splits(int n_tiles, int num_kb);
 int smallm_force_mt();
+int pdl_late();
 bool smallm_forced();                      // threshold set explicitly through the test hook
 
 template <int MT, bool BLK, typename OutT>
@@ -350,21 +356,10 @@ int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallM
   const int num_kb = ceil_div(p.K, 128);
   const int S = smallm_pick_splits(n_tiles, num_kb);
   p.kb_per_split = ceil_div(num_kb, S);
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(n_tiles * S, 1, 1);
-  cfg.blockDim = dim3(192, 1, 1);
-  cfg.dynamicSmemBytes = C::SMEM_BYTES;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = S;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  p.pdl_late = pdl_late();
   {
     ScopedKernelTimer timer(timer_name, st);
-    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
+    B200_CUDA_OK(launch_kernel(kern, dim3(n_tiles * S), dim3(192), C::SMEM_BYTES, st, S, pdl_family(p.M, kPdlGemmSmall), tw, tx, p));
   }
   B200_CHECK_LAUNCH("fp8_gemm_smallm_kernel");
   return 0;

@@ -56,6 +56,8 @@ fp8_quant_per_token_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __rest
                            const float* __restrict__ static_scale, int K, float eps) {
   constexpr bool STATIC = MODE == 1;
   __shared__ float red[32];
+  griddep_wait();
+  griddep_launch_dependents();
   const int m = blockIdx.x;
   const T* row = x + m * ldx;
   uint8_t* out = q + m * ldq;
@@ -101,6 +103,8 @@ __global__ void __launch_bounds__(256)
 fp8_quant_group128_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __restrict__ q,
                           int64_t ldq, float* __restrict__ scales, int64_t s_row, int64_t s_col,
                           int M, int groups_per_row, float eps) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int64_t gid = static_cast<int64_t>(blockIdx.x) * 16 + (threadIdx.x >> 4);
   const int lane = threadIdx.x & 15;
   const int64_t total = static_cast<int64_t>(M) * groups_per_row;
@@ -151,9 +155,9 @@ int b200_fp8_quant_per_token(const void* x, int64_t ldx, void* q, int64_t ldq, f
   ScopedKernelTimer timer("fp8_quant", st);
   const int threads = K >= 2048 ? 256 : 128;
 #define LAUNCH(T, MODE)                                                                          \
-  fp8_quant_per_token_kernel<T, MODE><<<M, threads, 0, st>>>(static_cast<const T*>(x), ldx,      \
-                                                             static_cast<uint8_t*>(q), ldq,      \
-                                                             scales, static_scale, K, eps)
+  B200_CUDA_OK(launch_kernel(fp8_quant_per_token_kernel<T, MODE>, dim3(M), dim3(threads), 0, st, 1, pdl_family(M, kPdlQuant), \
+                             static_cast<const T*>(x), ldx, static_cast<uint8_t*>(q), ldq, scales,  \
+                             static_scale, K, eps))
   if (dtype == B200_BF16) {
     if (static_scale) LAUNCH(__nv_bfloat16, 1);
     else if (use_division) LAUNCH(__nv_bfloat16, 2);
@@ -184,13 +188,14 @@ int b200_fp8_quant_group128(const void* x, int64_t ldx, void* q, int64_t ldq, fl
   const int64_t total = static_cast<int64_t>(M) * gpr;
   const unsigned blocks = static_cast<unsigned>((total + 15) / 16);
   if (dtype == B200_BF16)
-    fp8_quant_group128_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
-        static_cast<const __nv_bfloat16*>(x), ldx, static_cast<uint8_t*>(q), ldq, scales,
-        scale_row_stride, scale_col_stride, M, gpr, eps);
+    B200_CUDA_OK(launch_kernel(fp8_quant_group128_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0,
+                               st, 1, pdl_family(M, kPdlQuant), static_cast<const __nv_bfloat16*>(x), ldx,
+                               static_cast<uint8_t*>(q), ldq, scales, scale_row_stride,
+                               scale_col_stride, M, gpr, eps));
   else
-    fp8_quant_group128_kernel<__half><<<blocks, 256, 0, st>>>(
-        static_cast<const __half*>(x), ldx, static_cast<uint8_t*>(q), ldq, scales,
-        scale_row_stride, scale_col_stride, M, gpr, eps);
+    B200_CUDA_OK(launch_kernel(fp8_quant_group128_kernel<__half>, dim3(blocks), dim3(256), 0, st, 1, pdl_family(M, kPdlQuant),
+                               static_cast<const __half*>(x), ldx, static_cast<uint8_t*>(q), ldq,
+                               scales, scale_row_stride, scale_col_stride, M, gpr, eps));
   B200_CHECK_LAUNCH("fp8_quant_group128_kernel");
   return 0;
 }

@@ -120,6 +120,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  griddep_wait();  // activations / scales come from the previous kernel
+  griddep_launch_dependents();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -273,7 +275,7 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
   const int grid = tiles < sms ? tiles : sms;
   {
     ScopedKernelTimer timer(timer_name, st);
-    kern<<<grid, C::THREADS, C::SMEM_BYTES, st>>>(ta, tb, ep);
+    B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, 1, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));
   }
   B200_CHECK_LAUNCH("gemm_tn_kernel");
   return 0;

@@ -12,6 +12,8 @@ __global__ void kv_write_kernel(const char* __restrict__ k, const char* __restri
                                 int64_t k_stride, int64_t v_stride, char* __restrict__ k_cache,
                                 char* __restrict__ v_cache, const int64_t* __restrict__ loc,
                                 int num_tokens, int k_row_bytes, int v_row_bytes) {
+  griddep_wait();
+  griddep_launch_dependents();
   const bool is_v = blockIdx.y != 0;
   const char* src = is_v ? v : k;
   char* dst = is_v ? v_cache : k_cache;
@@ -36,6 +38,8 @@ __global__ void kv_indices_kernel(const int32_t* __restrict__ req_to_token, int6
                                   const int32_t* __restrict__ kv_indptr,
                                   const int32_t* __restrict__ kv_start,
                                   int32_t* __restrict__ kv_indices) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int b = blockIdx.x;
   const int64_t row = req_pool_indices[b];
   const int start = kv_start ? kv_start[b] : 0;
@@ -68,6 +72,7 @@ int b200_kv_write(const void* k, const void* v, int64_t k_token_stride_bytes,
                    static_cast<uintptr_t>(k_row_bytes) | static_cast<uintptr_t>(v_row_bytes);
   const int max_row = k_row_bytes > v_row_bytes ? k_row_bytes : v_row_bytes;
   ScopedKernelTimer timer("kv_write", st);
+  cudaError_t lerr = cudaSuccess;
   auto launch = [&](auto vec_tag) {
     using Vec = decltype(vec_tag);
     const int64_t total = static_cast<int64_t>(num_tokens) * (max_row / sizeof(Vec));
@@ -76,16 +81,17 @@ int b200_kv_write(const void* k, const void* v, int64_t k_token_stride_bytes,
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
     dim3 grid(static_cast<unsigned>(blocks), 2);
-    kv_write_kernel<Vec><<<grid, threads, 0, st>>>(
-        static_cast<const char*>(k), static_cast<const char*>(v), k_token_stride_bytes,
-        v_token_stride_bytes, static_cast<char*>(k_cache), static_cast<char*>(v_cache), loc,
-        num_tokens, k_row_bytes, v_row_bytes);
+    lerr = launch_kernel(kv_write_kernel<Vec>, grid, dim3(threads), 0, st, 1, pdl_family(num_tokens, kPdlOther),
+                         static_cast<const char*>(k), static_cast<const char*>(v),
+                         k_token_stride_bytes, v_token_stride_bytes, static_cast<char*>(k_cache),
+                         static_cast<char*>(v_cache), loc, num_tokens, k_row_bytes, v_row_bytes);
   };
   if ((bits & 15u) == 0) launch(uint4{});
   else if ((bits & 7u) == 0) launch(uint2{});
   else if ((bits & 3u) == 0) launch(uint32_t{});
   else if ((bits & 1u) == 0) launch(uint16_t{});
   else launch(uint8_t{});
+  B200_CUDA_OK(lerr);
   B200_CHECK_LAUNCH("b200_kv_write");
   return 0;
 }
@@ -102,8 +108,9 @@ int b200_kv_indices(const int32_t* req_to_token, int64_t req_to_token_stride,
   // Few requests: spread each row over several CTAs so a lone long request still fills SMs.
   int per_req = bs >= 512 ? 1 : (bs >= 64 ? 4 : 16);
   dim3 grid(static_cast<unsigned>(bs), static_cast<unsigned>(per_req));
-  kv_indices_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      req_to_token, req_to_token_stride, req_pool_indices, lens, kv_indptr, kv_start, kv_indices);
+  B200_CUDA_OK(launch_kernel(kv_indices_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream),
+                             1, pdl_family(bs, kPdlOther), req_to_token, req_to_token_stride, req_pool_indices, lens, kv_indptr,
+                             kv_start, kv_indices));
   B200_CHECK_LAUNCH("b200_kv_indices");
   return 0;
 }

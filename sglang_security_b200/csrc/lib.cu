@@ -1,6 +1,7 @@
 // Library-level C-ABI entry points: version, error text, launch counter.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -10,6 +11,22 @@ namespace b200 {
 
 static thread_local char g_error[1024] = "";
 std::atomic<int64_t> g_launch_count{0};
+
+static int pdl_default() {
+  const char* v = std::getenv("B200_PDL");
+  if (!(v && *v)) return 0xff;
+  const int m = std::atoi(v);  // bit mask over PdlFamily; 1 is read as "all"
+  return m == 1 ? 0xff : m;
+}
+std::atomic<int> g_pdl_on{pdl_default()};
+
+int pdl_max_tokens() {
+  static int v = [] {
+    const char* e = std::getenv("B200_PDL_MAX_M");
+    return (e && *e) ? std::atoi(e) : 32;
+  }();
+  return v;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -99,7 +116,12 @@ int b200_timing_read(const char* name, int64_t* launches, double* total_ms) {
   return 0;
 }
 
-int b200_version(void) { return 1; }
+int b200_version(void) { return 2; }
+
+int b200_set_pdl(int on) {
+  const int prev = b200::g_pdl_on.exchange(on == 1 ? 0xff : on);
+  return prev;
+}
 
 const char* b200_last_error(void) { return b200::g_error; }
 

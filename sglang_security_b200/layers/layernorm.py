@@ -49,8 +49,16 @@ class RMSNorm(nn.Module):
         self.variance_epsilon = eps
 
     def _weight_like(self, x):
+        """Weight in the activation dtype (the reference multiplies the fp32-promoted weight,
+        layernorm.py:104; checkpoints store it in the model dtype, so the cast is exact).  The
+        cast copy is cached until the parameter changes."""
         w = self.weight.data
-        return w if w.dtype == x.dtype else w.to(x.dtype)
+        if w.dtype == x.dtype:
+            return w
+        key = (w.data_ptr(), w._version, x.dtype)
+        if getattr(self, "_wcast_key", None) != key:
+            self._wcast, self._wcast_key = w.to(x.dtype), key
+        return self._wcast
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None
                 ) -> Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]]:
