@@ -194,6 +194,17 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
                     const void* scales, const void* bias, void* out, int64_t ldc, int M, int N,
                     int K, int group_size, int dtype, void* stream);
 
+/* Decode-regime GEMV (1 <= M <= 16, N %% 32 == 0, group %% 16 == 0): the packed weights are streamed
+ * once from HBM (0.5 byte / element) and consumed by mma.sync as exact integers,
+ *   out[m,n] = sum_g s[g,n] * (sum_{k in g} x[m,k] w[k,n] - z[g,n] sum_{k in g} x[m,k]),
+ * split-K over a thread-block cluster with a fixed-order reduction.  Same operands as
+ * b200_w4a16_gemm, which dispatches here for M <= 16; b200_w4a16_gemv_config(max_m, splits) lets
+ * tests and sweeps force either kernel (max_m = 0: never, negative: defaults).                   */
+int b200_w4a16_gemv(const void* x, int64_t ldx, const void* qweight, const void* zeros,
+                    const void* scales, const void* bias, void* out, int64_t ldc, int M, int N,
+                    int K, int group_size, int dtype, void* stream);
+int b200_w4a16_gemv_config(int max_m, int splits);
+
 /* ---- steps either side of the GEMMs / attention ------------------ */
 /* (residual +) RMSNorm, optionally fused with the FP8 activation quantiser of the linear layer that
  * consumes it.  Replaces RMSNorm.forward (python/sglang/srt/layers/layernorm.py:61-108; oracle =

@@ -28,6 +28,9 @@
 
 namespace b200 {
 
+int w4a16_gemv_max_m();                                        // w4a16_gemv.cu
+bool w4a16_gemv_supported(int M, int N, int K, int group);
+
 template <typename T>
 struct W4Magic;
 template <>
@@ -470,6 +473,10 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
   B200_REQUIRE(aligned16(x) && ldx % 8 == 0 && aligned16(zeros) && aligned16(scales),
                "b200_w4a16_gemm: x/zeros/scales must be 16-byte aligned, ldx %% 8 == 0");
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, "b200_w4a16_gemm: dtype %d", dtype);
+  // decode regime: HBM-bound GEMV on the packed weights (w4a16_gemv.cu)
+  if (M <= w4a16_gemv_max_m() && w4a16_gemv_supported(M, N, K, group_size) && aligned16(qweight))
+    return b200_w4a16_gemv(x, ldx, qweight, zeros, scales, bias, out, ldc, M, N, K, group_size,
+                           dtype, stream);
   W4GemmParams p;
   p.qweight = static_cast<const uint32_t*>(qweight);
   p.zeros = zeros;

@@ -71,3 +71,9 @@ def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, zeros: torch.Tensor, scal
                                      _lib.current_stream())
     _lib.check(rc, "b200_w4a16_gemm")
     return out
+
+
+def w4a16_gemv_config(max_m: int = -1, splits: int = -1) -> None:
+    """Test/sweep hook (b200_w4a16_gemv_config): max_m = 0 keeps b200_w4a16_gemm on the tcgen05
+    kernel for every M, splits > 0 fixes the GEMV's split-K cluster size, negative = defaults."""
+    _lib.check(_lib.load().b200_w4a16_gemv_config(int(max_m), int(splits)), "b200_w4a16_gemv_config")

@@ -127,3 +127,77 @@ def test_gptq_linear_method(desc_act, dtype):
     err = (out.cpu().float() - ref.float()).abs()
     tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
     assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
+
+
+@pytest.fixture
+def gemv_cfg():
+    from sglang_security_b200.layers.quantization.w4a16_kernel import w4a16_gemv_config
+
+    yield w4a16_gemv_config
+    w4a16_gemv_config(-1, -1)
+
+
+def _prep(qweight, scales, qzeros, dtype):
+    from sglang_security_b200.layers.quantization.w4a16_kernel import unpack_zeros
+
+    return (qweight.cuda().contiguous(), unpack_zeros(qzeros.cuda(), dtype, True, False),
+            scales.cuda().contiguous())
+
+
+@pytest.mark.parametrize("m", [1, 2, 7, 8, 9, 16])
+@pytest.mark.parametrize("k,n,group,splits", [(512, 256, 128, 0), (5120, 3584, 128, 0),
+                                              (2560, 5120, 128, 3), (1024, 288, 64, 8),
+                                              (256, 32, 32, 2), (13824, 5120, 128, 0),
+                                              (640, 2048, 128, 8)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_w4a16_gemv_matches_oracle_and_tcgen05_kernel(m, k, n, group, splits, dtype, gemv_cfg):
+    """Decode-regime GEMV (integer MMA + per-group zero/scale correction, cluster split-K incl.
+    empty ranks and partial 256-column tiles) against x @ dequant (oracle) and against the tcgen05
+    dequant-GEMM on identical operands; two runs bit-identical (fixed reduction order)."""
+    from sglang_security_b200.layers.quantization.w4a16_kernel import w4a16_gemm
+
+    if m * k * n > 2 ** 31:
+        pytest.skip("oracle too slow")
+    qweight, scales, qzeros = _awq_layer(k, n, group, dtype, seed=m * 3 + k + n, realistic=(n % 128 == 0))
+    g = torch.Generator().manual_seed(m + n)
+    x = torch.randn((m, k), generator=g).to(dtype)
+    bias = torch.randn((n,), generator=g).to(dtype)
+    ref = O.w4a16_linear_oracle(x, O.awq_dequantize_oracle(qweight, scales, qzeros, group), bias)
+    qw, zb, sc = _prep(qweight, scales, qzeros, dtype)
+    gemv_cfg(16, splits)
+    out = w4a16_gemm(x.cuda(), qw, zb, sc, group, bias.cuda())
+    assert torch.equal(out, w4a16_gemm(x.cuda(), qw, zb, sc, group, bias.cuda()))
+    gemv_cfg(0, -1)
+    out_big = w4a16_gemm(x.cuda(), qw, zb, sc, group, bias.cuda())
+    err = (out.cpu().float() - ref.float()).abs()
+    tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
+    assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
+    # the GEMV skips the per-weight 16-bit rounding of the dequantised value: it is at least as
+    # close to the exact fp64 result as the dequant-GEMM
+    w_exact = (O.unpack_awq_int4(qweight).double() -
+               O.unpack_awq_int4(qzeros).double().repeat_interleave(group, 0)) * \
+        scales.double().repeat_interleave(group, 0)
+    exact = x.double() @ w_exact + bias.double()
+    e_gemv = (out.cpu().double() - exact).abs().mean().item()
+    e_big = (out_big.cpu().double() - exact).abs().mean().item()
+    assert e_gemv <= 1.05 * e_big + 1e-6, (e_gemv, e_big)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_w4a16_gemv_integer_exact(dtype, gemv_cfg):
+    """INT4 unpacking through the GEMV is exact: unit scales and small-integer activations make
+    every partial sum an integer below 2^24 (fp32-exact) and the result fit the 16-bit output."""
+    from sglang_security_b200.layers.quantization.w4a16_kernel import w4a16_gemm
+
+    k, n, group, m = 256, 512, 64, 5
+    qweight = _rand_i32((k, n // 8), 31)
+    qzeros = _rand_i32((k // group, n // 8), 32)
+    scales = torch.ones((k // group, n), dtype=dtype)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(-1, 2, (m, k), generator=g).to(dtype)   # -1, 0, 1
+    w = O.unpack_awq_int4(qweight).long() - O.unpack_awq_int4(qzeros).long().repeat_interleave(group, 0)
+    exact = x.long() @ w                                      # |.| <= 256 * 15
+    qw, zb, sc = _prep(qweight, scales, qzeros, dtype)
+    gemv_cfg(16, 2)
+    out = w4a16_gemm(x.cuda(), qw, zb, sc, group)
+    assert torch.equal(out.cpu(), exact.to(dtype))
