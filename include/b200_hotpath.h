@@ -240,6 +240,50 @@ int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void
                        int native_rounding, void* k_cache, void* v_cache, int64_t cache_row_stride,
                        const int64_t* loc, int T, int Hq, int Hkv, int D, int dtype, void* stream);
 
+/* ---- tensor-parallel all-reduce over NVLink peer memory ------------------------------------- */
+/* Replaces the reference's custom all-reduce for decode-sized messages: host class CustomAllreduce
+ * (python/sglang/srt/distributed/device_communicators/custom_all_reduce.py:146-510; buffers are
+ * cudaMalloc'ed, exported with cudaIpcGetMemHandle and all-gathered, :303-326), kernels
+ * sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:127-225, called from GroupCoordinator.all_reduce
+ * (parallel_state.py:398-461).  One process per GPU; every rank allocates ONE symmetric buffer of
+ * b200_comm_buffer_bytes(world, max_bytes) with b200_comm_alloc (zero-filled; `handle_out`
+ * receives b200_comm_handle_bytes() bytes to send to the peers through torch.distributed), opens
+ * the peers' handles with b200_comm_open and builds the communicator from the `world` pointers
+ * (own buffer at index `rank`).  Tests may pass `world` buffers of ONE device and drive each rank
+ * from its own stream.  All ranks must issue the same sequence of collective calls. */
+int b200_comm_handle_bytes(void);
+size_t b200_comm_buffer_bytes(int world, size_t max_bytes);
+int b200_comm_alloc(size_t bytes, void** ptr, void* handle_out);
+int b200_comm_open(const void* handle, void** ptr);
+int b200_comm_close(void* ptr);
+int b200_comm_free(void* ptr);
+int b200_comm_create(int rank, int world, void* const* peer_bufs, size_t buf_bytes,
+                     void** comm_out);
+int b200_comm_destroy(void* comm);
+/* Largest message (bytes) one call can reduce (= one receive slot). */
+size_t b200_comm_max_bytes(const void* comm);
+/* out = sum over ranks of in (fp32 accumulation in rank order => bit-identical on every rank, one
+ * rounding); one-shot: every rank pushes its vector into all peers' slots, flags, local reduce.
+ * in may equal out.  numel * sizeof(dtype) must be a multiple of 16 (custom_all_reduce.py:418).  */
+int b200_comm_all_reduce(void* comm, const void* in, void* out, int64_t numel, int dtype,
+                         void* stream);
+
+/* Row-parallel linear = GEMM -> all-reduce (RowParallelLinear.forward, layers/linear.py:1277-1299)
+ * as ONE kernel in the decode regime (M <= 128): the swap-AB small-M kernel's epilogue pushes its
+ * scaled bf16/f16 tile to every TP peer, waits for the peers' copies of the same tile and stores
+ * their rank-ordered fp32 sum, so the transfer of one tile overlaps the weight streaming of the
+ * others.  Result = round(sum_r float(round(out_r))) exactly.  Larger M: big-tile GEMM followed by
+ * b200_comm_all_reduce in place (out must then be contiguous, ldc == N).  Arguments as the
+ * un-fused entry points; bias must be passed on rank 0 only (linear.py:1290).                  */
+int b200_fp8_gemm_rowcol_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
+                            const float* sa, int sa_stride, const float* sb, int sb_stride,
+                            const void* bias, void* out, int64_t ldc, int M, int N, int K,
+                            int out_dtype, void* stream);
+int b200_fp8_gemm_block128_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
+                              const float* as, int64_t as_row_stride, int64_t as_col_stride,
+                              const float* bs, int64_t bs_row_stride, const void* bias, void* out,
+                              int64_t ldc, int M, int N, int K, int out_dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,23 @@ _SIGNATURES = {
     "b200_fp8_gemm_block128": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
                                        c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_comm_handle_bytes": (c_int, []),
+    "b200_comm_buffer_bytes": (c_size_t, [c_int, c_size_t]),
+    "b200_comm_alloc": (c_int, [c_size_t, ctypes.POINTER(c_void_p), c_void_p]),
+    "b200_comm_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "b200_comm_close": (c_int, [c_void_p]),
+    "b200_comm_free": (c_int, [c_void_p]),
+    "b200_comm_create": (c_int, [c_int, c_int, ctypes.POINTER(c_void_p), c_size_t,
+                                 ctypes.POINTER(c_void_p)]),
+    "b200_comm_destroy": (c_int, [c_void_p]),
+    "b200_comm_max_bytes": (c_size_t, [c_void_p]),
+    "b200_comm_all_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "b200_fp8_gemm_rowcol_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                        c_int, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
+                                        c_int, c_int, c_int, c_void_p]),
+    "b200_fp8_gemm_block128_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                          c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
+                                          c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv_config": (c_int, [c_int, c_int]),

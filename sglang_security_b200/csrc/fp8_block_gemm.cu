@@ -229,10 +229,11 @@ static int launch_block_gemm(const void* a, int64_t lda, const void* b, int64_t 
 
 extern "C" {
 
-int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ldb, const float* as,
-                           int64_t as_row_stride, int64_t as_col_stride, const float* bs,
-                           int64_t bs_row_stride, const void* bias, void* out, int64_t ldc, int M,
-                           int N, int K, int out_dtype, void* stream) {
+static int fp8_gemm_block128_impl(const void* a, int64_t lda, const void* b, int64_t ldb,
+                                  const float* as, int64_t as_row_stride, int64_t as_col_stride,
+                                  const float* bs, int64_t bs_row_stride, const void* bias,
+                                  void* out, int64_t ldc, int M, int N, int K, int out_dtype,
+                                  void* stream, void* comm) {
   using namespace b200;
   if (M == 0 || N == 0) return 0;
   B200_REQUIRE(a && b && as && bs && out, "b200_fp8_gemm_block128: null pointer");
@@ -243,8 +244,13 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
                "b200_fp8_gemm_block128: out dtype %d", out_dtype);
   cudaStream_t st0 = static_cast<cudaStream_t>(stream);
   // (block-scaled: up to 64 tokens; the 128-token promotion loop is slower than the big tile)
-  if (M <= smallm_max_m() && (M <= 64 || smallm_forced())) {  // decode regime: weight streaming, swap-AB + cluster split-K
+  const bool fuse_ar = M <= 64 && comm_can_fuse(comm, M, N);
+  if (fuse_ar || (M <= smallm_max_m() && (M <= 64 || smallm_forced()))) {  // decode regime: weight streaming, swap-AB + cluster split-K
     SmallMParams sp = {};
+    if (fuse_ar) {
+      sp.use_comm = 1;
+      sp.comm = static_cast<const Comm*>(comm)->dev;
+    }
     sp.out = out;
     sp.ldc = ldc;
     sp.as = as;
@@ -271,8 +277,27 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
   p.N = N;
   p.K = K;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return out_dtype == B200_BF16 ? launch_block_gemm<__nv_bfloat16>(a, lda, b, ldb, p, st)
-                                : launch_block_gemm<__half>(a, lda, b, ldb, p, st);
+  const int rc = out_dtype == B200_BF16 ? launch_block_gemm<__nv_bfloat16>(a, lda, b, ldb, p, st)
+                                        : launch_block_gemm<__half>(a, lda, b, ldb, p, st);
+  if (rc || !comm) return rc;
+  return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);
+}
+
+int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ldb, const float* as,
+                           int64_t as_row_stride, int64_t as_col_stride, const float* bs,
+                           int64_t bs_row_stride, const void* bias, void* out, int64_t ldc, int M,
+                           int N, int K, int out_dtype, void* stream) {
+  return fp8_gemm_block128_impl(a, lda, b, ldb, as, as_row_stride, as_col_stride, bs, bs_row_stride,
+                                bias, out, ldc, M, N, K, out_dtype, stream, nullptr);
+}
+
+int b200_fp8_gemm_block128_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
+                              const float* as, int64_t as_row_stride, int64_t as_col_stride,
+                              const float* bs, int64_t bs_row_stride, const void* bias, void* out,
+                              int64_t ldc, int M, int N, int K, int out_dtype, void* stream) {
+  B200_REQUIRE(comm, "b200_fp8_gemm_block128_ar: null communicator");
+  return fp8_gemm_block128_impl(a, lda, b, ldb, as, as_row_stride, as_col_stride, bs, bs_row_stride,
+                                bias, out, ldc, M, N, K, out_dtype, stream, comm);
 }
 
 }  // extern "C"

@@ -109,6 +109,24 @@ int smallm_pick_splits(int n_tiles, int num_kb) {
   return s;
 }
 
+// Row-parallel fusion: the small-M kernel can reduce across the TP group in its epilogue when the
+// dense [M, N] partial fits one receive slot and the grid fits the flag table.
+bool comm_can_fuse(const void* comm, int M, int N) {
+  if (!comm || M > 128) return false;
+  const Comm* c = static_cast<const Comm*>(comm);
+  return static_cast<uint64_t>(M) * N * 2 <= c->dev.slot_bytes &&
+         ceil_div(N, 128) * 8 <= kCommMaxBlocks;
+}
+
+// Unfused tail for the big-tile kernels: in-place one-shot all-reduce of out[M, N] (ldc == N) or
+// an error asking the caller to use NCCL when the message exceeds the communicator's slot.
+int comm_all_reduce_rows(void* comm, void* out, int64_t ldc, int M, int N, int dtype,
+                         void* stream) {
+  B200_REQUIRE(ldc == N, "fused all-reduce needs a contiguous output (ldc %lld != N %d)",
+               static_cast<long long>(ldc), N);
+  return b200_comm_all_reduce(comm, out, out, static_cast<int64_t>(M) * N, dtype, stream);
+}
+
 }  // namespace b200
 
 extern "C" {
@@ -121,10 +139,10 @@ int b200_fp8_gemm_smallm_config(int max_m, int splits) {
   return 0;
 }
 
-int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
-                         int sa_stride, const float* sb, int sb_stride, const void* bias,
-                         void* out, int64_t ldc, int M, int N, int K, int out_dtype,
-                         void* stream) {
+static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64_t ldb,
+                               const float* sa, int sa_stride, const float* sb, int sb_stride,
+                               const void* bias, void* out, int64_t ldc, int M, int N, int K,
+                               int out_dtype, void* stream, void* comm) {
   using namespace b200;
   if (M == 0 || N == 0) return 0;
   B200_REQUIRE(a && b && out, "b200_fp8_gemm_rowcol: null pointer");
@@ -150,8 +168,13 @@ int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb,
   // big-tile kernel (profiles/r01_gemm_decode.json): always for M <= 64; for 64 < M <= 128 only when
   // K is long (down_proj) — the per-SM TMA row rate (128 weight rows + MT token rows per K block)
   // makes MT = 128 cost as much as a full 128x128 tile.
-  if (M <= smallm_max_m() && (M <= 64 || K >= 8192 || smallm_forced())) {
+  const bool fuse_ar = comm_can_fuse(comm, M, N);
+  if (fuse_ar || (M <= smallm_max_m() && (M <= 64 || K >= 8192 || smallm_forced()))) {
     SmallMParams sp = {};
+    if (fuse_ar) {
+      sp.use_comm = 1;
+      sp.comm = static_cast<const Comm*>(comm)->dev;
+    }
     sp.out = out;
     sp.ldc = ldc;
     sp.sa = sa;
@@ -167,12 +190,33 @@ int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb,
   // Tile choice: 128x256 when there is enough work to fill the SMs with it, else 128x128.
   const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);
   const bool big = tiles256 >= device_sm_count();
+  int rc;
   if (out_dtype == B200_BF16) {
-    return big ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm")
-               : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm");
-  }
-  return big ? launch_gemm_tn<kKindFp8, 256, 4, __half>(a, lda, b, ldb, ep, st, "fp8_gemm")
+    rc = big ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm")
+             : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm");
+  } else {
+    rc = big ? launch_gemm_tn<kKindFp8, 256, 4, __half>(a, lda, b, ldb, ep, st, "fp8_gemm")
              : launch_gemm_tn<kKindFp8, 128, 6, __half>(a, lda, b, ldb, ep, st, "fp8_gemm");
+  }
+  if (rc || !comm) return rc;
+  return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);
+}
+
+int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
+                         int sa_stride, const float* sb, int sb_stride, const void* bias,
+                         void* out, int64_t ldc, int M, int N, int K, int out_dtype,
+                         void* stream) {
+  return fp8_gemm_rowcol_impl(a, lda, b, ldb, sa, sa_stride, sb, sb_stride, bias, out, ldc, M, N, K,
+                              out_dtype, stream, nullptr);
+}
+
+int b200_fp8_gemm_rowcol_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
+                            const float* sa, int sa_stride, const float* sb, int sb_stride,
+                            const void* bias, void* out, int64_t ldc, int M, int N, int K,
+                            int out_dtype, void* stream) {
+  B200_REQUIRE(comm, "b200_fp8_gemm_rowcol_ar: null communicator");
+  return fp8_gemm_rowcol_impl(a, lda, b, ldb, sa, sa_stride, sb, sb_stride, bias, out, ldc, M, N, K,
+                              out_dtype, stream, comm);
 }
 
 }  // extern "C"

@@ -22,6 +22,7 @@
 //     native_w8a8_block_fp8_matmul, test_block_fp8.py:276-325).
 #pragma once
 
+#include "comm.cuh"
 #include "gemm_tc.cuh"
 
 namespace b200 {
@@ -41,7 +42,17 @@ struct SmallMParams {
   int M, N, K;
   int kb_per_split;
   int pdl_late;  // trigger dependents after the main loop instead of right after the dependency wait
+  // Row-parallel fusion (RowParallelLinear.forward, linear.py:1277-1299): when use_comm != 0 the
+  // epilogue does not store its tile but pushes it (bf16/f16, already scaled, bias on rank 0 only)
+  // into every tensor-parallel peer's receive slot over NVLink, then sums the `world` partials of
+  // the same tile in rank order (comm.cuh protocol) and stores the all-reduced result.
+  int use_comm;
+  CommDev comm;
 };
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(threads) : "memory");
+}
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -220,11 +231,20 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
     if (p.bias && n_ok) bn = to_float<OutT>(static_cast<const OutT*>(p.bias)[n]);
     const int tpr = ceil_div(p.M, static_cast<int>(S));  // tokens per rank (slots per source rank)
     const uint32_t push_base = smem_base + (rank * tpr * 128 + ch) * 4;
+    const uint32_t ar_epoch = p.use_comm ? comm_begin(p.comm) : 0u;
 
     auto finish = [&](int m, float v) {  // scales + bias + cast + store of one output element
       float sc = 1.f;
       if (!BLK) sc = (p.sa ? __ldg(p.sa + static_cast<int64_t>(m) * p.sa_stride) : 1.f) * sbn;
-      if (n_ok) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<OutT>(fmaf(v, sc, bn));
+      if (!n_ok) return;
+      const OutT o = from_float<OutT>(fmaf(v, sc, bn));
+      if (p.use_comm) {  // dense [M, N] partial into slot [my tp rank] of every rank (mine included)
+        const int64_t idx = static_cast<int64_t>(m) * p.N + n;
+        for (int r = 0; r < p.comm.world; ++r)
+          reinterpret_cast<OutT*>(comm_slot(p.comm, r, p.comm.rank, ar_epoch))[idx] = o;
+      } else {
+        out[static_cast<int64_t>(m) * p.ldc + n] = o;
+      }
     };
     // running (rank, slot) of token m = c*16 + j while the unrolled loops walk m upwards
     uint32_t dst_rank = 0, dst_slot = 0;
@@ -318,6 +338,29 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
         finish(m, sum);
       }
     }
+    if (p.use_comm) {
+      // tensor-parallel reduce of this CTA's outputs: tokens m = rank, rank + S, ... (all if S == 1)
+      named_bar_sync(1, 128);  // every push of this CTA has been issued
+      if (ch < p.comm.world) {
+        comm_signal(p.comm, ar_epoch, blockIdx.x, ch);
+        comm_wait(p.comm, ar_epoch, blockIdx.x, ch);
+      }
+      named_bar_sync(1, 128);
+      if (n_ok) {
+        for (int m = rank; m < p.M; m += S) {
+          const int64_t idx = static_cast<int64_t>(m) * p.N + n;
+          float sum = 0.f;
+          for (int r = 0; r < p.comm.world; ++r) {
+            const unsigned short u = __ldcg(
+                reinterpret_cast<const unsigned short*>(comm_slot(p.comm, p.comm.rank, r, ar_epoch)) + idx);
+            sum += to_float<OutT>(*reinterpret_cast<const OutT*>(&u));
+          }
+          out[static_cast<int64_t>(m) * p.ldc + n] = from_float<OutT>(sum);
+        }
+      }
+      named_bar_sync(1, 128);
+      if (ch == 0) comm_end(p.comm, ar_epoch, gridDim.x);
+    }
   }
   if (warp < 2 && S > 1) {  // producer / MMA warps take part in the two cluster barriers
     __syncwarp();
@@ -335,6 +378,8 @@ int smallm_pick_splits(int n_tiles, int num_kb);
 int smallm_force_mt();
 int pdl_late();
 bool smallm_forced();                      // threshold set explicitly through the test hook
+bool comm_can_fuse(const void* comm, int M, int N);
+int comm_all_reduce_rows(void* comm, void* out, int64_t ldc, int M, int N, int dtype, void* stream);
 
 template <int MT, bool BLK, typename OutT>
 int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallMParams p,

@@ -4,6 +4,7 @@ layers use in the reference (python/sglang/srt/distributed/communication_op.py:1
 parallel_state.py:398-461, 1047-1200): the all-reduce sits only at the row-parallel boundaries."""
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -12,14 +13,19 @@ import torch.distributed as dist
 _TP_GROUP: Optional[dist.ProcessGroup] = None
 _TP_SIZE = 1
 _TP_RANK = 0
+_TP_CA_COMM = None  # B200AllReduce: NVLink peer-memory all-reduce for decode-sized messages
 
 
 def initialize_model_parallel(tensor_model_parallel_size: int = 1,
-                              backend: Optional[str] = None) -> None:
-    """All ranks of the default group form ONE tensor-parallel group (pp = dp = 1 on this path)."""
-    global _TP_GROUP, _TP_SIZE, _TP_RANK
+                              backend: Optional[str] = None,
+                              use_custom_all_reduce: Optional[bool] = None) -> None:
+    """All ranks of the default group form ONE tensor-parallel group (pp = dp = 1 on this path).
+    `use_custom_all_reduce` (default: on for NCCL groups, env B200_CUSTOM_AR=0 turns it off)
+    builds the peer-memory communicator the way GroupCoordinator.__init__ builds `ca_comm`
+    (parallel_state.py:262-268)."""
+    global _TP_GROUP, _TP_SIZE, _TP_RANK, _TP_CA_COMM
     if tensor_model_parallel_size == 1:
-        _TP_GROUP, _TP_SIZE, _TP_RANK = None, 1, 0
+        _TP_GROUP, _TP_SIZE, _TP_RANK, _TP_CA_COMM = None, 1, 0, None
         return
     if not dist.is_initialized():
         raise RuntimeError("torch.distributed must be initialised before initialize_model_parallel")
@@ -29,11 +35,28 @@ def initialize_model_parallel(tensor_model_parallel_size: int = 1,
     _TP_GROUP = dist.group.WORLD
     _TP_SIZE = world
     _TP_RANK = dist.get_rank()
+    _TP_CA_COMM = None
+    if use_custom_all_reduce is None:
+        use_custom_all_reduce = (dist.get_backend() == "nccl"
+                                 and os.environ.get("B200_CUSTOM_AR", "1") != "0")
+    if use_custom_all_reduce:
+        from .device_communicators.b200_all_reduce import B200AllReduce
+
+        _TP_CA_COMM = B200AllReduce(_TP_GROUP, torch.device("cuda", torch.cuda.current_device()))
 
 
 def destroy_model_parallel() -> None:
-    global _TP_GROUP, _TP_SIZE, _TP_RANK
-    _TP_GROUP, _TP_SIZE, _TP_RANK = None, 1, 0
+    global _TP_GROUP, _TP_SIZE, _TP_RANK, _TP_CA_COMM
+    if _TP_CA_COMM is not None:
+        _TP_CA_COMM.close()
+    _TP_GROUP, _TP_SIZE, _TP_RANK, _TP_CA_COMM = None, 1, 0, None
+
+
+def get_tp_custom_all_reduce():
+    """The peer-memory communicator of the TP group (None when disabled / CPU / tp == 1)."""
+    if _TP_CA_COMM is not None and not _TP_CA_COMM.disabled:
+        return _TP_CA_COMM
+    return None
 
 
 def get_tensor_model_parallel_world_size() -> int:
@@ -45,9 +68,14 @@ def get_tensor_model_parallel_rank() -> int:
 
 
 def tensor_model_parallel_all_reduce(input_: torch.Tensor) -> torch.Tensor:
-    """Sum over the TP group (in place, like the NCCL path of GroupCoordinator.all_reduce)."""
+    """Sum over the TP group: out-of-place through the peer-memory communicator when the message
+    qualifies (GroupCoordinator.all_reduce, parallel_state.py:442-449), else in place over NCCL."""
     if _TP_SIZE == 1:
         return input_
+    if _TP_CA_COMM is not None and not _TP_CA_COMM.disabled:
+        out = _TP_CA_COMM.custom_all_reduce(input_)
+        if out is not None:
+            return out
     dist.all_reduce(input_, op=dist.ReduceOp.SUM, group=_TP_GROUP)
     return input_
 

@@ -13,6 +13,7 @@ from torch.nn import Parameter
 
 from ..distributed.parallel_state import (get_tensor_model_parallel_rank,
                                           get_tensor_model_parallel_world_size,
+                                          get_tp_custom_all_reduce,
                                           tensor_model_parallel_all_gather,
                                           tensor_model_parallel_all_reduce)
 from .quantization.base_config import LinearMethodBase, QuantizationConfig, set_weight_attrs
@@ -172,7 +173,18 @@ class RowParallelLinear(LinearBase):
             input_ = input_.chunk(self.tp_size, dim=-1)[self.tp_rank].contiguous()
         # bias is fused into the GEMM only on rank 0 so the all-reduce adds it exactly once
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
-        output = self.quant_method.apply(self, input_, bias=bias_)
         if self.reduce_results and self.tp_size > 1:
-            output = tensor_model_parallel_all_reduce(output)
+            comm = get_tp_custom_all_reduce()
+            if comm is not None and getattr(self.quant_method, "supports_fused_all_reduce", False):
+                # GEMM -> all-reduce as one call: the decode-regime kernel reduces in its epilogue
+                self.fused_all_reduce = comm
+                try:
+                    output = self.quant_method.apply(self, input_, bias=bias_)
+                finally:
+                    self.fused_all_reduce = None
+            else:
+                output = self.quant_method.apply(self, input_, bias=bias_)
+                output = tensor_model_parallel_all_reduce(output)
+        else:
+            output = self.quant_method.apply(self, input_, bias=bias_)
         return output, (self.bias if self.skip_bias_add else None)

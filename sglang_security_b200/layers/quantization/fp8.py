@@ -134,13 +134,19 @@ class Fp8LinearMethod(LinearMethodBase):
         if self.quant_config.activation_scheme == "static":
             layer.input_scale = Parameter(layer.input_scale.data.max(), requires_grad=False)
 
+    # RowParallelLinear.forward may hand the TP communicator over in `layer.fused_all_reduce`: the
+    # GEMM then returns the all-reduced output (one kernel in the decode regime).
+    supports_fused_all_reduce = True
+
     def apply(self, layer: torch.nn.Module, x: torch.Tensor,
               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        comm = getattr(layer, "fused_all_reduce", None)
         if self.block_quant:
             return apply_w8a8_block_fp8_linear(input=x, weight=layer.weight,
                                                block_size=self.quant_config.weight_block_size,
                                                weight_scale=layer.weight_scale_inv,
-                                               input_scale=None, bias=bias)
+                                               input_scale=None, bias=bias, comm=comm)
         return apply_fp8_linear(input=x, weight=layer.weight, weight_scale=layer.weight_scale,
                                 input_scale=layer.input_scale, bias=bias,
-                                cutlass_fp8_supported=True, use_per_token_if_dynamic=False)
+                                cutlass_fp8_supported=True, use_per_token_if_dynamic=False,
+                                comm=comm)

@@ -87,7 +87,7 @@ def per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: float = 1e-
 
 def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                   scales_b: torch.Tensor, out_dtype: torch.dtype,
-                  bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  bias: Optional[torch.Tensor] = None, comm=None) -> torch.Tensor:
     """out = (A @ B) * scales_a[:,None] * scales_b[None,:] (+ bias): A [M,K] row-major e4m3,
     B [K,N] COLUMN-major e4m3 (the `.t()` view of the [N,K] weight), as sgl_kernel.fp8_scaled_mm
     (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1071-1146)."""
@@ -105,17 +105,21 @@ def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tens
     sb = scales_b.reshape(-1).to(torch.float32)
     if bias is not None and bias.dtype != out_dtype:
         bias = bias.to(out_dtype)
-    rc = _lib.load().b200_fp8_gemm_rowcol(
-        mat_a.data_ptr(), mat_a.stride(0), mat_b.data_ptr(), mat_b.stride(1), sa.data_ptr(),
-        1 if sa.numel() > 1 else 0, sb.data_ptr(), 1 if sb.numel() > 1 else 0, _lib.ptr(bias),
-        out.data_ptr(), out.stride(0), m, n, k, _lib.dtype_code(out_dtype), _lib.current_stream())
-    _lib.check(rc, "b200_fp8_gemm_rowcol")
+    args = (mat_a.data_ptr(), mat_a.stride(0), mat_b.data_ptr(), mat_b.stride(1), sa.data_ptr(),
+            1 if sa.numel() > 1 else 0, sb.data_ptr(), 1 if sb.numel() > 1 else 0, _lib.ptr(bias),
+            out.data_ptr(), out.stride(0), m, n, k, _lib.dtype_code(out_dtype),
+            _lib.current_stream())
+    if comm is not None:  # row-parallel: GEMM + tensor-parallel all-reduce (fused for M <= 128)
+        _lib.check(_lib.load().b200_fp8_gemm_rowcol_ar(comm.handle, *args),
+                   "b200_fp8_gemm_rowcol_ar")
+    else:
+        _lib.check(_lib.load().b200_fp8_gemm_rowcol(*args), "b200_fp8_gemm_rowcol")
     return out
 
 
 def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, weight: torch.Tensor, scales_a: torch.Tensor,
                             scales_b: torch.Tensor, out_dtype: torch.dtype,
-                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                            bias: Optional[torch.Tensor] = None, comm=None) -> torch.Tensor:
     """Block-scaled GEMM: A [M,K] e4m3 with [M, K/128] scales (any strides), weight [N,K] e4m3
     (K contiguous) with [ceil(N/128), ceil(K/128)] scales -> [M,N] out_dtype
     (w8a8_block_fp8_matmul, fp8_kernel.py:774-891 / sgl_kernel.fp8_blockwise_scaled_mm)."""
@@ -134,12 +138,15 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, weight: torch.Tensor, scales_a:
     out = torch.empty((m, n), device=mat_a.device, dtype=out_dtype)
     if bias is not None and bias.dtype != out_dtype:
         bias = bias.to(out_dtype)
-    rc = _lib.load().b200_fp8_gemm_block128(
-        mat_a.data_ptr(), mat_a.stride(0), weight.data_ptr(), weight.stride(0), scales_a.data_ptr(),
-        scales_a.stride(0), scales_a.stride(1), scales_b.data_ptr(), scales_b.stride(0),
-        _lib.ptr(bias), out.data_ptr(), out.stride(0), m, n, k, _lib.dtype_code(out_dtype),
-        _lib.current_stream())
-    _lib.check(rc, "b200_fp8_gemm_block128")
+    args = (mat_a.data_ptr(), mat_a.stride(0), weight.data_ptr(), weight.stride(0),
+            scales_a.data_ptr(), scales_a.stride(0), scales_a.stride(1), scales_b.data_ptr(),
+            scales_b.stride(0), _lib.ptr(bias), out.data_ptr(), out.stride(0), m, n, k,
+            _lib.dtype_code(out_dtype), _lib.current_stream())
+    if comm is not None:
+        _lib.check(_lib.load().b200_fp8_gemm_block128_ar(comm.handle, *args),
+                   "b200_fp8_gemm_block128_ar")
+    else:
+        _lib.check(_lib.load().b200_fp8_gemm_block128(*args), "b200_fp8_gemm_block128")
     return out
 
 

@@ -42,16 +42,17 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
                      input_scale: Optional[torch.Tensor] = None,
                      input_scale_ub: Optional[torch.Tensor] = None,
                      bias: Optional[torch.Tensor] = None, cutlass_fp8_supported: bool = True,
-                     use_per_token_if_dynamic: bool = False) -> torch.Tensor:
+                     use_per_token_if_dynamic: bool = False, comm=None) -> torch.Tensor:
     """weight is the [K, N] column-major view of the e4m3 [N, K] weight; weight_scale has one
-    entry per output channel (or is a scalar)."""
+    entry per output channel (or is a scalar).  `comm` (a B200AllReduce) makes the GEMM reduce its
+    output across the tensor-parallel group (row-parallel layers)."""
     if weight_scale.numel() not in (1, weight.shape[1]):
         raise ValueError("B200 fp8 linear supports per-channel (or per-tensor) weight scales only")
     if isinstance(input, QuantizedActivation):
         if input_scale is not None or input.scale.shape[-1] != 1:
             raise ValueError("pre-quantised activation must be dynamic per-token for this layer")
         return fp8_scaled_mm(input.q, weight, input.scale, weight_scale, out_dtype=input.dtype,
-                             bias=bias)
+                             bias=bias, comm=comm)
     input_2d = input.reshape(-1, input.shape[-1])
     if input_2d.stride(-1) != 1:
         input_2d = input_2d.contiguous()
@@ -60,14 +61,15 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
         qinput, x_scale = static_quant_fp8(input_2d, input_scale, repeat_scale=False)
     else:
         qinput, x_scale = sglang_per_token_quant_fp8(input_2d)
-    output = fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)
+    output = fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias,
+                           comm=comm)
     return output.view(*output_shape)
 
 
 def apply_w8a8_block_fp8_linear(input: torch.Tensor, weight: torch.Tensor, block_size: List[int],
                                 weight_scale: torch.Tensor,
                                 input_scale: Optional[torch.Tensor] = None,
-                                bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                                bias: Optional[torch.Tensor] = None, comm=None) -> torch.Tensor:
     """Block-quantised linear: weight [N, K] e4m3 with [ceil(N/128), ceil(K/128)] fp32 scales,
     activations quantised per (token, 128-group) on the fly."""
     assert input_scale is None
@@ -75,14 +77,14 @@ def apply_w8a8_block_fp8_linear(input: torch.Tensor, weight: torch.Tensor, block
         raise ValueError(f"B200 block-fp8 linear supports 128x128 weight blocks, got {block_size}")
     if isinstance(input, QuantizedActivation):
         return fp8_blockwise_scaled_mm(input.q, weight, input.scale, weight_scale,
-                                       out_dtype=input.dtype, bias=bias)
+                                       out_dtype=input.dtype, bias=bias, comm=comm)
     input_2d = input.reshape(-1, input.shape[-1])
     if input_2d.stride(-1) != 1:
         input_2d = input_2d.contiguous()
     output_shape = [*input.shape[:-1], weight.shape[0]]
     q_input, x_scale = per_token_group_quant_fp8(input_2d, block_size[1], column_major_scales=False)
     output = fp8_blockwise_scaled_mm(q_input, weight, x_scale, weight_scale, out_dtype=input.dtype,
-                                     bias=bias)
+                                     bias=bias, comm=comm)
     return output.view(*output_shape)
 
 

@@ -69,7 +69,10 @@ class W8A8Fp8LinearMethod(LinearMethodBase):
             layer.weight_scale = Parameter(weight_scale.t().contiguous(), requires_grad=False)
             layer.input_scale = None
 
+    supports_fused_all_reduce = True  # see Fp8LinearMethod
+
     def apply(self, layer: torch.nn.Module, x: torch.Tensor,
               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         return apply_fp8_linear(x, layer.weight, layer.weight_scale, bias=bias,
-                                cutlass_fp8_supported=True)
+                                cutlass_fp8_supported=True,
+                                comm=getattr(layer, "fused_all_reduce", None))
