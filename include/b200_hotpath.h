@@ -279,6 +279,8 @@ int b200_fp8_gemm_rowcol_ar(void* comm, const void* a, int64_t lda, const void* 
                             const float* sa, int sa_stride, const float* sb, int sb_stride,
                             const void* bias, void* out, int64_t ldc, int M, int N, int K,
                             int out_dtype, void* stream);
+/* Largest M the *_ar entry points fuse (default 32, measured crossover; max 128; < 0 = default). */
+int b200_comm_fuse_config(int max_m);
 int b200_fp8_gemm_block128_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
                               const float* as, int64_t as_row_stride, int64_t as_col_stride,
                               const float* bs, int64_t bs_row_stride, const void* bias, void* out,

@@ -62,6 +62,7 @@ _SIGNATURES = {
     "b200_comm_destroy": (c_int, [c_void_p]),
     "b200_comm_max_bytes": (c_size_t, [c_void_p]),
     "b200_comm_all_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    "b200_comm_fuse_config": (c_int, [c_int]),
     "b200_fp8_gemm_rowcol_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                         c_int, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
                                         c_int, c_int, c_int, c_void_p]),

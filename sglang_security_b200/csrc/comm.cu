@@ -4,6 +4,7 @@
 // sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:203-225); larger messages stay on NCCL.
 #include "comm.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -99,6 +100,67 @@ all_reduce_oneshot_kernel(const CommDev c, const uint4* __restrict__ in, uint4* 
   if (threadIdx.x == 0) comm_end(c, e, gridDim.x);
 }
 
+// LL variant: every 16-byte input vector travels as four 8-byte {payload, epoch} words; the
+// receiver polls the words themselves (comm.cuh).  No barrier, no fence: one NVLink trip.
+template <typename T, bool kF32>
+__global__ void __launch_bounds__(128)
+all_reduce_ll_kernel(const CommDev c, const uint4* __restrict__ in, uint4* __restrict__ out,
+                     int64_t num_vec) {
+  griddep_wait();
+  griddep_launch_dependents();
+  const uint32_t e = comm_begin(c);
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t first = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (int64_t v = first; v < num_vec; v += stride) {
+    const uint4 x = in[v];
+    for (int i = 1; i < c.world; ++i) {
+      int p = c.rank + i;
+      if (p >= c.world) p -= c.world;
+      uint2* dst = comm_ll_slot(c, p, c.rank, e) + 4 * v;
+      ll_store2(dst, x.x, x.y, e);
+      ll_store2(dst + 2, x.z, x.w, e);
+    }
+  }
+  for (int64_t v = first; v < num_vec; v += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < c.world; ++r) {
+      uint4 x;
+      if (r == c.rank) {
+        x = in[v];
+      } else {
+        const uint2* src = comm_ll_slot(c, c.rank, r, e) + 4 * v;
+        const uint2 a = ll_load2(src, e), b = ll_load2(src + 2, e);
+        x = make_uint4(a.x, a.y, b.x, b.y);
+      }
+      if constexpr (kF32) {
+        acc[0] += __uint_as_float(x.x);
+        acc[1] += __uint_as_float(x.y);
+        acc[2] += __uint_as_float(x.z);
+        acc[3] += __uint_as_float(x.w);
+      } else {
+        accum8<T>(acc, x);
+      }
+    }
+    if constexpr (kF32)
+      out[v] = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
+                          __float_as_uint(acc[3]));
+    else
+      out[v] = pack8<T>(acc);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) comm_end(c, e, gridDim.x);
+}
+
+// LL is used while its doubled wire size is cheaper than the flag protocol's fence + flag round
+// trip (env B200_COMM_LL_MAX overrides the payload threshold in bytes).
+static int64_t ll_max_bytes() {
+  static int64_t v = [] {
+    const char* e = std::getenv("B200_COMM_LL_MAX");
+    return (e && *e) ? std::atoll(e) : static_cast<int64_t>(512 * 1024);
+  }();
+  return v;
+}
+
 }  // namespace b200
 
 extern "C" {
@@ -107,7 +169,7 @@ int b200_comm_handle_bytes(void) { return static_cast<int>(sizeof(cudaIpcMemHand
 
 size_t b200_comm_buffer_bytes(int world, size_t max_bytes) {
   const size_t slot = (max_bytes + 1023) / 1024 * 1024;
-  return b200::kCommDataOffset + 2 * static_cast<size_t>(world) * slot;
+  return b200::kCommDataOffset + 4 * static_cast<size_t>(world) * slot;  // 2 LL + 2 raw parities
 }
 
 int b200_comm_alloc(size_t bytes, void** ptr, void* handle_out) {
@@ -154,7 +216,7 @@ int b200_comm_create(int rank, int world, void* const* peer_bufs, size_t buf_byt
   B200_REQUIRE(world >= 2 && world <= kCommMaxRanks && rank >= 0 && rank < world,
                "b200_comm_create: rank %d / world %d (2..%d ranks supported)", rank, world,
                kCommMaxRanks);
-  B200_REQUIRE(buf_bytes > kCommDataOffset + 2 * static_cast<size_t>(world) * 1024,
+  B200_REQUIRE(buf_bytes > kCommDataOffset + 4 * static_cast<size_t>(world) * 1024,
                "b200_comm_create: buffer of %zu bytes is too small", buf_bytes);
   Comm* c = new Comm();
   for (int r = 0; r < world; ++r) {
@@ -168,7 +230,7 @@ int b200_comm_create(int rank, int world, void* const* peer_bufs, size_t buf_byt
   for (int r = world; r < kCommMaxRanks; ++r) c->dev.peer[r] = nullptr;
   c->dev.rank = rank;
   c->dev.world = world;
-  c->dev.slot_bytes = ((buf_bytes - kCommDataOffset) / (2 * static_cast<size_t>(world))) / 1024 * 1024;
+  c->dev.slot_bytes = ((buf_bytes - kCommDataOffset) / (4 * static_cast<size_t>(world))) / 1024 * 1024;
   c->buf_bytes = buf_bytes;
   *comm_out = c;
   return 0;
@@ -200,6 +262,30 @@ int b200_comm_all_reduce(void* comm, const void* in, void* out, int64_t numel, i
                "b200_comm_all_reduce: %lld bytes exceed the communicator's max_size %llu",
                static_cast<long long>(bytes), static_cast<unsigned long long>(c->dev.slot_bytes));
   const int64_t num_vec = bytes / 16;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const uint4* i4 = static_cast<const uint4*>(in);
+  uint4* o4 = static_cast<uint4*>(out);
+  if (bytes <= ll_max_bytes() && static_cast<uint64_t>(2 * bytes) <= c->dev.slot_bytes) {
+    int64_t ctas64 = (num_vec + 127) / 128;
+    const int64_t cap = 4 * static_cast<int64_t>(device_sm_count());
+    const int ctas = static_cast<int>(ctas64 < cap ? ctas64 : cap);
+    {
+      ScopedKernelTimer timer("all_reduce_ll", st);
+      cudaError_t err;
+      if (dtype == B200_BF16)
+        err = launch_kernel(all_reduce_ll_kernel<__nv_bfloat16, false>, dim3(ctas), dim3(128), 0, st,
+                            1, kPdlOther, c->dev, i4, o4, num_vec);
+      else if (dtype == B200_F16)
+        err = launch_kernel(all_reduce_ll_kernel<__half, false>, dim3(ctas), dim3(128), 0, st, 1,
+                            kPdlOther, c->dev, i4, o4, num_vec);
+      else
+        err = launch_kernel(all_reduce_ll_kernel<float, true>, dim3(ctas), dim3(128), 0, st, 1,
+                            kPdlOther, c->dev, i4, o4, num_vec);
+      B200_CUDA_OK(err);
+    }
+    B200_CHECK_LAUNCH("all_reduce_ll_kernel");
+    return 0;
+  }
   // 8 KiB per CTA (2 vectors per thread) up to 2 CTAs per SM, then grow the per-CTA share.
   int64_t vec_per_cta = 512;
   const int64_t sm2 = 2 * static_cast<int64_t>(device_sm_count());
@@ -207,9 +293,6 @@ int b200_comm_all_reduce(void* comm, const void* in, void* out, int64_t numel, i
   if ((num_vec + vec_per_cta - 1) / vec_per_cta > max_ctas)
     vec_per_cta = (num_vec + max_ctas - 1) / max_ctas;
   const int ctas = static_cast<int>((num_vec + vec_per_cta - 1) / vec_per_cta);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const uint4* i4 = static_cast<const uint4*>(in);
-  uint4* o4 = static_cast<uint4*>(out);
   {
     ScopedKernelTimer timer("all_reduce_oneshot", st);
     cudaError_t err;

@@ -10,7 +10,17 @@
 //                done   (local)   CTAs of the running call that have finished
 //                flags[2][8][kCommMaxBlocks]  written by PEERS: flags[e&1][src][cta] = e once CTA
 //                                 `cta` of rank `src` has pushed its part of call e
+//   ll[2][world][slot_bytes]      low-latency area: 8-byte words {32-bit payload, 32-bit flag = e}
 //   data[2][world][slot_bytes]    data[e&1][src] = partial of rank `src` for call e
+//
+// Two protocols share the epoch counter:
+//  * LL (messages whose doubled size fits a slot): the flag travels WITH the data — every 8-byte
+//    word a rank pushes carries the call's epoch in its upper half (8-byte stores are single-copy
+//    atomic, also over NVLink), the receiver polls the word itself until the flag matches.  One
+//    one-way NVLink trip, no fence, no barrier; costs 2x the wire bytes.  Flags always sit in the
+//    odd 32-bit words of the LL area, whatever the layout of the call, and the area is never used
+//    for raw data, so a stale word can never look valid.
+//  * flag protocol (larger messages), below.
 //
 // Protocol of call e (= epoch + 1), identical grid on every rank, CTA c:
 //   push    the CTA writes its part of the partial into data[e&1][my rank] of EVERY peer
@@ -53,9 +63,53 @@ struct CommDev {
 __device__ __forceinline__ CommHeader* comm_header(const CommDev& c, int r) {
   return reinterpret_cast<CommHeader*>(c.peer[r]);
 }
-// data[e&1][src] in the buffer of rank `dst`
+// data[e&1][src] in the buffer of rank `dst` (raw area comes after the 2*world LL slots)
 __device__ __forceinline__ uint8_t* comm_slot(const CommDev& c, int dst, int src, uint32_t e) {
-  return c.peer[dst] + kCommDataOffset + ((e & 1u) * c.world + src) * c.slot_bytes;
+  return c.peer[dst] + kCommDataOffset + ((2u + (e & 1u)) * c.world + src) * c.slot_bytes;
+}
+// ll[e&1][src] in the buffer of rank `dst`
+__device__ __forceinline__ uint2* comm_ll_slot(const CommDev& c, int dst, int src, uint32_t e) {
+  return reinterpret_cast<uint2*>(c.peer[dst] + kCommDataOffset +
+                                  ((e & 1u) * c.world + src) * c.slot_bytes);
+}
+// Push two LL words {d0,e},{d1,e} with one 16-byte store (either 8-byte half is self-validating).
+__device__ __forceinline__ void ll_store2(uint2* dst, uint32_t d0, uint32_t d1, uint32_t e) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};\n" ::"l"(dst), "r"(d0), "r"(e),
+               "r"(d1), "r"(e)
+               : "memory");
+}
+__device__ __forceinline__ void ll_store1(uint2* dst, uint32_t d0, uint32_t e) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};\n" ::"l"(dst), "r"(d0), "r"(e) : "memory");
+}
+__device__ __forceinline__ void ll_timeout_check(uint64_t& t0) {
+  uint64_t t1;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t1));
+  if (t0 == 0) t0 = t1;
+  if (t1 - t0 > kCommTimeoutNs) __trap();
+}
+// Poll two adjacent LL words until both carry epoch e; returns their payloads.
+__device__ __forceinline__ uint2 ll_load2(const uint2* src, uint32_t e) {
+  uint32_t d0, f0, d1, f1;
+  uint64_t t0 = 0;
+  while (true) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];\n"
+                 : "=r"(d0), "=r"(f0), "=r"(d1), "=r"(f1)
+                 : "l"(src)
+                 : "memory");
+    if (f0 == e && f1 == e) break;
+    ll_timeout_check(t0);
+  }
+  return make_uint2(d0, d1);
+}
+__device__ __forceinline__ uint32_t ll_load1(const uint2* src, uint32_t e) {
+  uint32_t d0, f0;
+  uint64_t t0 = 0;
+  while (true) {
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(d0), "=r"(f0) : "l"(src) : "memory");
+    if (f0 == e) break;
+    ll_timeout_check(t0);
+  }
+  return d0;
 }
 __device__ __forceinline__ uint32_t comm_begin(const CommDev& c) {
   return *reinterpret_cast<volatile uint32_t*>(&comm_header(c, c.rank)->epoch) + 1u;

@@ -262,7 +262,9 @@ static int fp8_gemm_block128_impl(const void* a, int64_t lda, const void* b, int
     sp.M = M;
     sp.N = N;
     sp.K = K;
-    return dispatch_smallm<true>(a, lda, b, ldb, sp, out_dtype, st0, "fp8_block_gemm_smallm");
+    const int rc = dispatch_smallm<true>(a, lda, b, ldb, sp, out_dtype, st0, "fp8_block_gemm_smallm");
+    if (rc || !comm || fuse_ar) return rc;
+    return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);
   }
   BlockGemmParams p;
   p.out = out;

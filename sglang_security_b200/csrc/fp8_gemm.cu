@@ -111,10 +111,25 @@ int smallm_pick_splits(int n_tiles, int num_kb) {
 
 // Row-parallel fusion: the small-M kernel can reduce across the TP group in its epilogue when the
 // dense [M, N] partial fits one receive slot and the grid fits the flag table.
+// Policy measured at TP = 2 on B200 (profiles/r01_bench_allreduce_tp2.json): fusing wins while the
+// swap-AB kernel itself is the right GEMM (M <= 32: 7.7 vs 8.2 us at M = 1, 13.1 vs 15.4 us at
+// M = 32, against GEMM + stand-alone LL all-reduce); above that the big-tile GEMM + all-reduce is
+// faster.  b200_comm_fuse_config / B200_COMM_FUSE_MAX_M override.
+static std::atomic<int> g_fuse_max_m{-1};
+static int fuse_max_m() {
+  int v = g_fuse_max_m.load(std::memory_order_relaxed);
+  if (v < 0) {
+    v = env_int("B200_COMM_FUSE_MAX_M", 32);
+    g_fuse_max_m.store(v, std::memory_order_relaxed);
+  }
+  return v > 128 ? 128 : v;
+}
+
 bool comm_can_fuse(const void* comm, int M, int N) {
-  if (!comm || M > 128) return false;
+  if (!comm || M > fuse_max_m()) return false;
   const Comm* c = static_cast<const Comm*>(comm);
-  return static_cast<uint64_t>(M) * N * 2 <= c->dev.slot_bytes &&
+  // LL words: one 8-byte word per (token pair, channel), pairs padded per cluster rank (S <= 8)
+  return static_cast<uint64_t>(M / 2 + 8) * N * 8 <= c->dev.slot_bytes &&
          ceil_div(N, 128) * 8 <= kCommMaxBlocks;
 }
 
@@ -130,6 +145,13 @@ int comm_all_reduce_rows(void* comm, void* out, int64_t ldc, int M, int N, int d
 }  // namespace b200
 
 extern "C" {
+
+/* Largest M for which the *_ar entry points fuse the reduce into the GEMM epilogue (< 0 restores
+ * the default). */
+int b200_comm_fuse_config(int max_m) {
+  b200::g_fuse_max_m.store(max_m, std::memory_order_relaxed);
+  return 0;
+}
 
 /* Test/sweep hook: max_m < 0 / splits < 0 re-read the environment defaults. */
 int b200_fp8_gemm_smallm_config(int max_m, int splits) {
@@ -185,7 +207,9 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
     sp.M = M;
     sp.N = N;
     sp.K = K;
-    return dispatch_smallm<false>(a, lda, b, ldb, sp, out_dtype, st, "fp8_gemm_smallm");
+    const int rc = dispatch_smallm<false>(a, lda, b, ldb, sp, out_dtype, st, "fp8_gemm_smallm");
+    if (rc || !comm || fuse_ar) return rc;
+    return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);
   }
   // Tile choice: 128x256 when there is enough work to fill the SMs with it, else 128x128.
   const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);

@@ -232,16 +232,28 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
     const int tpr = ceil_div(p.M, static_cast<int>(S));  // tokens per rank (slots per source rank)
     const uint32_t push_base = smem_base + (rank * tpr * 128 + ch) * 4;
     const uint32_t ar_epoch = p.use_comm ? comm_begin(p.comm) : 0u;
+    // Fused tensor-parallel reduce (LL protocol, comm.cuh): the thread's outputs come in a fixed
+    // sequence (tokens 0,1,2,.. if S == 1, else rank, rank+S, ..); two consecutive ones are packed
+    // into one 32-bit payload and pushed as an 8-byte {payload, epoch} word to word index
+    // (pair * S + cluster rank) * N + n of slot [my tp rank] on EVERY tp rank (mine included).
+    uint32_t ll_stash = 0;
+    int ll_cnt = 0;
+    auto ll_push = [&](uint32_t payload) {
+      const int64_t widx = (static_cast<int64_t>(ll_cnt >> 1) * S + rank) * p.N + n;
+      for (int r = 0; r < p.comm.world; ++r)
+        ll_store1(comm_ll_slot(p.comm, r, p.comm.rank, ar_epoch) + widx, payload, ar_epoch);
+    };
 
     auto finish = [&](int m, float v) {  // scales + bias + cast + store of one output element
       float sc = 1.f;
       if (!BLK) sc = (p.sa ? __ldg(p.sa + static_cast<int64_t>(m) * p.sa_stride) : 1.f) * sbn;
       if (!n_ok) return;
       const OutT o = from_float<OutT>(fmaf(v, sc, bn));
-      if (p.use_comm) {  // dense [M, N] partial into slot [my tp rank] of every rank (mine included)
-        const int64_t idx = static_cast<int64_t>(m) * p.N + n;
-        for (int r = 0; r < p.comm.world; ++r)
-          reinterpret_cast<OutT*>(comm_slot(p.comm, r, p.comm.rank, ar_epoch))[idx] = o;
+      if (p.use_comm) {
+        const uint32_t bits = *reinterpret_cast<const unsigned short*>(&o);
+        if (ll_cnt & 1) ll_push(ll_stash | (bits << 16));
+        else ll_stash = bits;
+        ++ll_cnt;
       } else {
         out[static_cast<int64_t>(m) * p.ldc + n] = o;
       }
@@ -339,24 +351,22 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
       }
     }
     if (p.use_comm) {
-      // tensor-parallel reduce of this CTA's outputs: tokens m = rank, rank + S, ... (all if S == 1)
-      named_bar_sync(1, 128);  // every push of this CTA has been issued
-      if (ch < p.comm.world) {
-        comm_signal(p.comm, ar_epoch, blockIdx.x, ch);
-        comm_wait(p.comm, ar_epoch, blockIdx.x, ch);
-      }
-      named_bar_sync(1, 128);
-      if (n_ok) {
-        for (int m = rank; m < p.M; m += S) {
-          const int64_t idx = static_cast<int64_t>(m) * p.N + n;
-          float sum = 0.f;
-          for (int r = 0; r < p.comm.world; ++r) {
-            const unsigned short u = __ldcg(
-                reinterpret_cast<const unsigned short*>(comm_slot(p.comm, p.comm.rank, r, ar_epoch)) + idx);
-            sum += to_float<OutT>(*reinterpret_cast<const OutT*>(&u));
-          }
-          out[static_cast<int64_t>(m) * p.ldc + n] = from_float<OutT>(sum);
+      if (ll_cnt & 1) ll_push(ll_stash);  // odd tail: upper half is padding
+      const int pairs = (ll_cnt + 1) >> 1;
+      for (int pi = 0; pi < pairs; ++pi) {
+        const int64_t widx = (static_cast<int64_t>(pi) * S + rank) * p.N + n;
+        float s0 = 0.f, s1 = 0.f;
+        for (int r = 0; r < p.comm.world; ++r) {  // rank order: bit-identical on every tp rank
+          const uint32_t w = ll_load1(comm_ll_slot(p.comm, p.comm.rank, r, ar_epoch) + widx, ar_epoch);
+          const float2 f = unpack2<OutT>(w);
+          s0 += f.x;
+          s1 += f.y;
         }
+        const int q0 = 2 * pi, q1 = 2 * pi + 1;
+        const int m0 = S == 1 ? q0 : static_cast<int>(rank) + q0 * static_cast<int>(S);
+        const int m1 = S == 1 ? q1 : static_cast<int>(rank) + q1 * static_cast<int>(S);
+        out[static_cast<int64_t>(m0) * p.ldc + n] = from_float<OutT>(s0);
+        if (q1 < ll_cnt) out[static_cast<int64_t>(m1) * p.ldc + n] = from_float<OutT>(s1);
       }
       named_bar_sync(1, 128);
       if (ch == 0) comm_end(p.comm, ar_epoch, gridDim.x);

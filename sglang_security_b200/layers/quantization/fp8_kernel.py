@@ -156,3 +156,9 @@ def fp8_gemm_smallm_config(max_m: int = -1, splits: int = -1) -> None:
     values restore the defaults."""
     _lib.check(_lib.load().b200_fp8_gemm_smallm_config(int(max_m), int(splits)),
                "b200_fp8_gemm_smallm_config")
+
+
+def comm_fuse_config(max_m: int = -1) -> None:
+    """Largest token count for which row-parallel GEMMs reduce in their epilogue
+    (b200_comm_fuse_config; negative = measured default)."""
+    _lib.check(_lib.load().b200_comm_fuse_config(int(max_m)), "b200_comm_fuse_config")

@@ -108,16 +108,21 @@ def _rand_fp8(shape, g, amp=448.0):
 
 @pytest.mark.parametrize("world,n,k", [(2, 4096, 2048), (2, 1024, 7168), (4, 1024, 1024),
                                        (8, 512, 512)])
-@pytest.mark.parametrize("m", [1, 7, 16, 33, 64, 100, 128, 200])
+@pytest.mark.parametrize("m", [1, 7, 16, 33, 64, 100, 128])
 def test_fp8_rowcol_gemm_fused_all_reduce_local(world, n, k, m):
-    """Row-parallel FP8 GEMM: fused epilogue all-reduce == oracle sum of the per-rank outputs."""
-    from sglang_security_b200.layers.quantization.fp8_kernel import (fp8_gemm_smallm_config,
+    """Row-parallel FP8 GEMM: fused epilogue all-reduce == oracle sum of the per-rank outputs.
+    (M > 128 = big-tile GEMM followed by the stand-alone all-reduce is covered by the multi-process
+    test only: with every rank on ONE device the early-launched, spinning all-reduce CTAs of rank 0
+    can keep rank 1's GEMM from being scheduled.)"""
+    from sglang_security_b200.layers.quantization.fp8_kernel import (comm_fuse_config,
+                                                                    fp8_gemm_smallm_config,
                                                                     fp8_scaled_mm)
 
     grp = _group(world)
     # the fused path always takes the swap-AB kernel for M <= 128; make the un-fused per-rank
     # outputs come from the same kernel (same split-K grouping => same fp32 partial sums)
     fp8_gemm_smallm_config(max_m=128)
+    comm_fuse_config(128)  # fuse for every M the kernel supports, whatever the tuned policy is
     try:
         g = torch.Generator().manual_seed(m * 31 + n + world)
         a = [_rand_fp8((m, k), g, 8.0).cuda() for _ in range(world)]
@@ -137,15 +142,18 @@ def test_fp8_rowcol_gemm_fused_all_reduce_local(world, n, k, m):
                 assert torch.equal(outs[r].cpu(), ref), (r, (outs[r].cpu().float() - ref.float()).abs().max())
     finally:
         fp8_gemm_smallm_config(-1, -1)
+        comm_fuse_config(-1)
         grp.close()
 
 
 @pytest.mark.parametrize("world,n,k", [(2, 4096, 1024), (4, 1024, 2048)])
-@pytest.mark.parametrize("m", [1, 16, 48, 64, 150])
+@pytest.mark.parametrize("m", [1, 16, 48, 64])
 def test_fp8_block_gemm_fused_all_reduce_local(world, n, k, m):
-    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_blockwise_scaled_mm
+    from sglang_security_b200.layers.quantization.fp8_kernel import (comm_fuse_config,
+                                                                    fp8_blockwise_scaled_mm)
 
     grp = _group(world)
+    comm_fuse_config(128)
     try:
         g = torch.Generator().manual_seed(m * 17 + n + world)
         a = [_rand_fp8((m, k), g, 8.0).cuda() for _ in range(world)]
@@ -162,6 +170,7 @@ def test_fp8_block_gemm_fused_all_reduce_local(world, n, k, m):
         for r in range(world):
             assert torch.equal(outs[r].cpu(), ref), r
     finally:
+        comm_fuse_config(-1)
         grp.close()
 
 
@@ -212,14 +221,32 @@ def _mp_worker(rank, world, port, out_dir):
     from sglang_security_b200.layers.quantization.fp8_kernel import fp8_gemm_smallm_config
 
     fp8_gemm_smallm_config(max_m=128)  # un-fused reference GEMM through the same swap-AB kernel
-    for m in [1, 16, 64, 128, 300]:
-        x_full = torch.randn((m, inter), generator=g).to(torch.bfloat16)
-        x = x_full[:, rank * (inter // world):(rank + 1) * (inter // world)].contiguous().cuda()
-        y, _ = layer(x)                                         # fused path
-        part = layer.quant_method.apply(layer, x, bias=layer.bias if rank == 0 else None)
-        parts = [torch.empty_like(part) for _ in range(world)]
-        dist.all_gather(parts, part)
-        assert torch.equal(y.cpu(), OA.row_parallel_linear_oracle(parts)), m
+    from sglang_security_b200.layers.quantization.fp8_kernel import (comm_fuse_config,
+                                                                    fp8_blockwise_scaled_mm)
+
+    for fuse_max in (-1, 128):  # tuned policy, then fusion forced for every supported M
+        comm_fuse_config(fuse_max)
+        for m in [1, 16, 64, 128, 300]:
+            x_full = torch.randn((m, inter), generator=g).to(torch.bfloat16)
+            x = x_full[:, rank * (inter // world):(rank + 1) * (inter // world)].contiguous().cuda()
+            y, _ = layer(x)                                         # GEMM + all-reduce in one call
+            part = layer.quant_method.apply(layer, x, bias=layer.bias if rank == 0 else None)
+            parts = [torch.empty_like(part) for _ in range(world)]
+            dist.all_gather(parts, part)
+            assert torch.equal(y.cpu(), OA.row_parallel_linear_oracle(parts)), (fuse_max, m)
+        # block-scaled kernel: fused (M <= 64) and big tile + stand-alone all-reduce (M = 150)
+        k = 1024
+        wq = ((torch.rand((hidden, k), generator=g) - 0.5) * 8).to(FP8).cuda()
+        ws = (torch.rand((hidden // 128, k // 128), generator=g) * 1e-2 + 1e-3).cuda()
+        for m in [4, 64, 150]:
+            aq = ((torch.rand((m, k), generator=g) - 0.5) * 16).to(FP8).cuda()
+            a_s = (torch.rand((m, k // 128), generator=g) * 1e-2 + 1e-3).cuda()
+            y = fp8_blockwise_scaled_mm(aq, wq, a_s, ws, torch.bfloat16, comm=comm)
+            part = fp8_blockwise_scaled_mm(aq, wq, a_s, ws, torch.bfloat16)
+            parts = [torch.empty_like(part) for _ in range(world)]
+            dist.all_gather(parts, part)
+            assert torch.equal(y.cpu(), OA.row_parallel_linear_oracle(parts)), ("block", fuse_max, m)
+    comm_fuse_config(-1)
     dist.barrier()
     ps.destroy_model_parallel()
     open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
