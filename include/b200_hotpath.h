@@ -65,6 +65,17 @@ int b200_kv_write(const void* k, const void* v, int64_t k_token_stride_bytes,
                   const int64_t* loc, int num_tokens, int k_row_bytes, int v_row_bytes,
                   void* stream);
 
+/* Quantising variant for an FP8 (e4m3) pool, `--kv-cache-dtype fp8_e4m3` (model_runner.py:845-858):
+ * replaces the cast branch of set_kv_buffer (memory_pool.py:390-400) in one kernel, bit-exact with
+ * torch: has_scale != 0 -> x = round_to_src_dtype(x / scale) (the in-place div_), then
+ * `.to(float8_e4m3fn)` (round-to-nearest-even, NO saturation: |x| > 464 and NaN -> NaN byte).
+ * k, v  [num_tokens, row_elems] bf16/f16, token strides in ELEMENTS; caches [slots, row_elems] bytes.
+ * Unlike the reference the source k/v tensors are left untouched.                               */
+int b200_kv_write_fp8(const void* k, const void* v, int64_t k_token_stride,
+                      int64_t v_token_stride, void* k_cache, void* v_cache, const int64_t* loc,
+                      int num_tokens, int row_elems, float k_scale, float v_scale, int has_scale,
+                      int dtype, void* stream);
+
 /* ---- request -> token index gather ------------------------------------ */
 /* Replaces create_flashinfer_kv_indices_triton (python/sglang/srt/layers/attention/utils.py:5-41):
  *   kv_indices[kv_indptr[b] + i] = req_to_token[req_pool_indices[b], kv_start[b] + i], i < lens[b]
@@ -96,6 +107,20 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
                      const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
                      int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
                      void* workspace, size_t workspace_bytes, int num_splits, void* stream);
+
+/* Same contract over an FP8 (e4m3) KV pool (k_cache/v_cache rows of D bytes, kv_row_stride in
+ * bytes): o = v_scale * softmax(scale * k_scale * q.K8^T) @ V8 — FlashInfer-backend semantics
+ * (flashinfer_backend.py:499-509); pass 1.0 for the Triton backend's scale-free reading
+ * (triton_backend.py:808-833).  q/o dtype bf16 or f16.  Splits are aligned to
+ * b200_attn_decode_fp8kv_split_align() tokens.  Half the HBM bytes of the 16-bit pool.          */
+int b200_attn_decode_fp8kv_split_align(void);
+int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                           const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
+                           int Hq, int Hkv, int D, int Dv, float scale, float logit_cap,
+                           float k_scale, float v_scale, int dtype, void* workspace,
+                           size_t workspace_bytes, int num_splits, void* stream);
 
 /* Merge of split-KV partial states (replaces _fwd_kernel_stage2, decode_attention.py:497-557,
  * and merge_state_v2, sgl-kernel/csrc/attention/merge_attn_states.cu): exposed for tests.

@@ -36,16 +36,21 @@ def _attend(q, k, v, scale, causal_offset=None, logit_cap=0.0):
 
 
 def decode_attention_oracle(q, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens, scale,
-                            logit_cap=0.0):
-    """q [bs, Hq, D] -> o [bs, Hq, Dv] in q.dtype."""
+                            logit_cap=0.0, k_scale=1.0, v_scale=1.0):
+    """q [bs, Hq, D] -> o [bs, Hq, Dv] in q.dtype.
+    FP8 KV pool (k_cache/v_cache of dtype float8_e4m3fn): the stored values are de-quantised as
+    value * k_scale / value * v_scale — the FlashInfer-backend semantics of the reference
+    (flashinfer_backend.py:499-509; the Triton backend is the k_scale = v_scale = 1 case,
+    triton_backend.py:808-833); torch_native itself cannot run SDPA on fp8 tensors, so this is the
+    unmodified torch_native math applied to the de-quantised cache."""
     bs, hq, _ = q.shape
     dv = v_cache.shape[-1]
     o = torch.empty((bs, hq, dv), dtype=q.dtype)
     for b in range(bs):
         n = int(seq_lens[b])
         tok = req_to_token[int(req_pool_indices[b]), :n].long()
-        k = k_cache[tok].float().transpose(0, 1)   # [Hkv, n, D]
-        v = v_cache[tok].float().transpose(0, 1)
+        k = k_cache[tok].float().transpose(0, 1) * k_scale   # [Hkv, n, D]
+        v = v_cache[tok].float().transpose(0, 1) * v_scale
         out = _attend(q[b].float().unsqueeze(1), k, v, scale, None, logit_cap)  # [Hq, 1, Dv]
         o[b] = out.squeeze(1).to(q.dtype)
     return o

@@ -24,23 +24,31 @@ class OracleMHATokenToKVPool:
         self.head_num, self.head_dim, self.layer_num = head_num, head_dim, layer_num
         self.start_layer = 0
         shape = (size + page_size, head_num, head_dim)
-        self.k_buffer = [torch.zeros(shape, dtype=dtype) for _ in range(layer_num)]
-        self.v_buffer = [torch.zeros(shape, dtype=dtype) for _ in range(layer_num)]
+        # fp8 caches are stored as bytes (memory_pool.py:119-123: index_put has no fp8 kernel)
+        self.store_dtype = (torch.uint8 if dtype in (torch.float8_e5m2, torch.float8_e4m3fn)
+                            else dtype)
+        self.k_buffer = [torch.zeros(shape, dtype=self.store_dtype) for _ in range(layer_num)]
+        self.v_buffer = [torch.zeros(shape, dtype=self.store_dtype) for _ in range(layer_num)]
 
-    def get_key_buffer(self, layer_id):
-        return self.k_buffer[layer_id - self.start_layer]
+    def get_key_buffer(self, layer_id):  # memory_pool.py:359-365
+        t = self.k_buffer[layer_id - self.start_layer]
+        return t.view(self.dtype) if self.store_dtype != self.dtype else t
 
-    def get_value_buffer(self, layer_id):
-        return self.v_buffer[layer_id - self.start_layer]
+    def get_value_buffer(self, layer_id):  # memory_pool.py:367-373
+        t = self.v_buffer[layer_id - self.start_layer]
+        return t.view(self.dtype) if self.store_dtype != self.dtype else t
 
     def set_kv_buffer(self, layer, loc, cache_k, cache_v, k_scale=None, v_scale=None):
-        # memory_pool.py:378-412 (bf16/f16 cache: plain index_put of the rows)
+        # memory_pool.py:378-412 (bf16/f16 cache: plain index_put of the rows; fp8 cache: in-place
+        # divide by the scale, cast, store the bytes)
         if cache_k.dtype != self.dtype:
             if k_scale is not None:
                 cache_k.div_(k_scale)
             if v_scale is not None:
                 cache_v.div_(v_scale)
             cache_k, cache_v = cache_k.to(self.dtype), cache_v.to(self.dtype)
+        if self.store_dtype != self.dtype:  # memory_pool.py:398-400
+            cache_k, cache_v = cache_k.view(self.store_dtype), cache_v.view(self.store_dtype)
         self.k_buffer[layer.layer_id - self.start_layer][loc] = cache_k
         self.v_buffer[layer.layer_id - self.start_layer][loc] = cache_v
 

@@ -25,6 +25,13 @@ _SIGNATURES = {
     "b200_timing_read": (c_int, [c_char_p, ctypes.POINTER(c_int64), ctypes.POINTER(ctypes.c_double)]),
     "b200_kv_write": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                               c_int, c_int, c_int, c_void_p]),
+    "b200_kv_write_fp8": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+                                  c_int, c_int, c_float, c_float, c_int, c_int, c_void_p]),
+    "b200_attn_decode_fp8kv_split_align": (c_int, []),
+    "b200_attn_decode_fp8kv": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                       c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
+                                       c_int, c_int, c_int, c_float, c_float, c_float, c_float,
+                                       c_int, c_void_p, c_size_t, c_int, c_void_p]),
     "b200_kv_indices": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_int, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

@@ -44,6 +44,7 @@ struct DecodeParams {
   int num_splits;
   float qk_scale;   // scale*log2e, or plain scale when logit_cap > 0
   float logit_cap;  // <= 0: disabled
+  float v_scale;    // FP8 KV pool only: output multiplier (k_scale is folded into qk_scale)
   int pdl_late;
 };
 
@@ -133,6 +134,10 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
   asm("cvt.rn.f16x2.f32 %0, %1, %2;\n" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
+
+}  // namespace b200
+#include "attn_decode_fp8.cuh"
+namespace b200 {
 
 // HI: the tile holds more than 8 heads (rows 8..15 of the MMA are live).
 template <typename T, int D, int NT, int STAGES, int NW, bool HI>
@@ -480,6 +485,55 @@ static int dispatch_decode(const DecodeParams& p, int D, int G, cudaStream_t st)
   return 1;
 }
 
+// ---- FP8 KV pool: 32-token tiles (same 8 KiB per stage as the bf16 kernel's 16-token tiles) ------
+constexpr int kNT8 = 32;
+static int decode_align_fp8kv() { return kNW * kNT8; }
+
+static int fp8kv_stages() {
+  static int v = [] {
+    const char* e = std::getenv("B200_FP8KV_STAGES");
+    const int s = (e && *e) ? std::atoi(e) : 2;
+    return s == 3 ? 3 : 2;
+  }();
+  return v;
+}
+
+template <typename T, int D, bool HI, int ST>
+static int launch_decode_fp8kv_st(const DecodeParams& p, cudaStream_t st) {
+  using C = Fp8KvCfg<D, kNT8, ST, kNW>;
+  auto kern = attn_decode_fp8kv_kernel<T, D, kNT8, ST, kNW, HI>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+    attr_done = true;
+  }
+  dim3 grid(p.num_splits, p.Hkv * p.head_tiles, p.bs);
+  {
+    ScopedKernelTimer timer("attn_decode_fp8kv", st);
+    B200_CUDA_OK(launch_kernel(kern, grid, dim3(C::THREADS), C::SMEM_BYTES, st, 1,
+                               pdl_family(p.bs, kPdlAttn), p));
+  }
+  B200_CHECK_LAUNCH("attn_decode_fp8kv_kernel");
+  return 0;
+}
+
+template <typename T, int D, bool HI>
+static int launch_decode_fp8kv(const DecodeParams& p, cudaStream_t st) {
+  return fp8kv_stages() == 3 ? launch_decode_fp8kv_st<T, D, HI, 3>(p, st)
+                             : launch_decode_fp8kv_st<T, D, HI, 2>(p, st);
+}
+
+template <typename T>
+static int dispatch_decode_fp8kv(const DecodeParams& p, int D, int G, cudaStream_t st) {
+  if (D == 128)
+    return G > 8 ? launch_decode_fp8kv<T, 128, true>(p, st) : launch_decode_fp8kv<T, 128, false>(p, st);
+  if (D == 64)
+    return G > 8 ? launch_decode_fp8kv<T, 64, true>(p, st) : launch_decode_fp8kv<T, 64, false>(p, st);
+  set_error("b200_attn_decode_fp8kv: unsupported head_dim %d (supported: 64, 128)", D);
+  return 1;
+}
+
 }  // namespace b200
 
 extern "C" {
@@ -565,6 +619,7 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
   p.head_tiles = ceil_div(p.group, G);
   p.num_splits = num_splits;
   p.logit_cap = logit_cap;
+  p.v_scale = 1.f;
   p.qk_scale = logit_cap > 0.f ? scale : scale * kLog2e;
   { static const char* e = std::getenv("B200_PDL_LATE"); p.pdl_late = e ? std::atoi(e) : 1; }
   p.part_o = static_cast<float*>(workspace);
@@ -577,6 +632,70 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
   if (num_splits > 1)
     return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
                            decode_align(), dtype, stream);
+  return 0;
+}
+
+int b200_attn_decode_fp8kv_split_align(void) { return b200::decode_align_fp8kv(); }
+
+int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                           const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
+                           int Hq, int Hkv, int D, int Dv, float scale, float logit_cap,
+                           float k_scale, float v_scale, int dtype, void* workspace,
+                           size_t workspace_bytes, int num_splits, void* stream) {
+  using namespace b200;
+  if (bs == 0) return 0;
+  B200_REQUIRE(q && k_cache && v_cache && o && req_to_token && req_pool_indices && seq_lens,
+               "b200_attn_decode_fp8kv: null pointer");
+  B200_REQUIRE(bs > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0,
+               "b200_attn_decode_fp8kv: bad head config bs=%d Hq=%d Hkv=%d", bs, Hq, Hkv);
+  B200_REQUIRE(D == Dv, "b200_attn_decode_fp8kv: qk_head_dim (%d) != v_head_dim (%d)", D, Dv);
+  B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16,
+               "b200_attn_decode_fp8kv: q/o dtype %d not supported (bf16/f16)", dtype);
+  B200_REQUIRE(num_splits >= 1 && num_splits <= 1024, "b200_attn_decode_fp8kv: bad num_splits %d",
+               num_splits);
+  B200_REQUIRE(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && q_stride % 8 == 0 &&
+                   kv_row_stride % 16 == 0,
+               "b200_attn_decode_fp8kv: q/k_cache/v_cache must be 16-byte aligned, q_stride %% 8 == 0 "
+               "and kv_row_stride %% 16 == 0");
+  B200_REQUIRE(bs <= 65535 && Hkv * 8 <= 65535, "b200_attn_decode_fp8kv: grid too large");
+  B200_REQUIRE(k_scale > 0.f && v_scale > 0.f, "b200_attn_decode_fp8kv: scales must be positive");
+  const size_t need = b200_attn_decode_workspace_bytes(bs, Hq, Dv, num_splits);
+  B200_REQUIRE(num_splits == 1 || (workspace && workspace_bytes >= need),
+               "b200_attn_decode_fp8kv: workspace too small (%zu < %zu)", workspace_bytes, need);
+  DecodeParams p;
+  p.q = q;
+  p.q_stride = q_stride;
+  p.k_cache = k_cache;
+  p.v_cache = v_cache;
+  p.kv_row_stride = kv_row_stride;
+  p.o = o;
+  p.o_stride = o_stride;
+  p.req_to_token = req_to_token;
+  p.rtt_stride = req_to_token_stride;
+  p.req_pool_indices = req_pool_indices;
+  p.seq_lens = seq_lens;
+  p.bs = bs;
+  p.Hq = Hq;
+  p.Hkv = Hkv;
+  p.group = Hq / Hkv;
+  const int G = tile_heads(p.group);
+  p.head_tiles = ceil_div(p.group, G);
+  p.num_splits = num_splits;
+  p.logit_cap = logit_cap;
+  p.v_scale = v_scale;
+  p.qk_scale = (logit_cap > 0.f ? scale : scale * kLog2e) * k_scale;
+  { static const char* e = std::getenv("B200_PDL_LATE"); p.pdl_late = e ? std::atoi(e) : 1; }
+  p.part_o = static_cast<float*>(workspace);
+  p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, st)
+                                    : dispatch_decode_fp8kv<__half>(p, D, G, st);
+  if (rc) return rc;
+  if (num_splits > 1)
+    return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
+                           decode_align_fp8kv(), dtype, stream);
   return 0;
 }
 

@@ -6,6 +6,8 @@
 #include "fp8_gemm_smallm.cuh"
 
 #include <cstdlib>
+#include <mutex>
+#include <vector>
 
 namespace b200 {
 
@@ -106,6 +108,82 @@ int smallm_pick_splits(int n_tiles, int num_kb) {
   if (s > 8) s = 8;
   if (s > num_kb) s = num_kb;
   if (s < 1) s = 1;
+  return s;
+}
+
+// ---- split-K scratch for the big-tile kernel ------------------------------------------------------
+struct SplitKScratch {
+  int dev;
+  cudaStream_t st;
+  float* ws;
+  size_t ws_bytes;
+  unsigned* counters;
+  int counter_cap;
+};
+static std::mutex g_splitk_mu;
+static std::vector<SplitKScratch> g_splitk;
+
+bool splitk_workspace(cudaStream_t st, size_t ws_bytes, int tiles, float** ws, unsigned** counters) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  std::lock_guard<std::mutex> lk(g_splitk_mu);
+  SplitKScratch* e = nullptr;
+  for (auto& x : g_splitk)
+    if (x.dev == dev && x.st == st) e = &x;
+  if (e && e->ws_bytes >= ws_bytes && e->counter_cap >= tiles) {
+    *ws = e->ws;
+    *counters = e->counters;
+    return true;
+  }
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
+    // a captured stream is usually a side stream: share the scratch of any stream of this device
+    // that is large enough (launches on different streams of one process are ordered by the
+    // framework around graph capture), never allocate during capture
+    for (auto& x : g_splitk)
+      if (x.dev == dev && x.ws_bytes >= ws_bytes && x.counter_cap >= tiles) {
+        *ws = x.ws;
+        *counters = x.counters;
+        return true;
+      }
+    (void)cudaGetLastError();
+    return false;
+  }
+  const size_t want = ws_bytes < (static_cast<size_t>(32) << 20) ? (static_cast<size_t>(32) << 20) : ws_bytes;
+  const int ccap = tiles < 1024 ? 1024 : tiles;
+  float* nws = nullptr;
+  unsigned* nc = nullptr;
+  if (cudaMalloc(&nws, want) != cudaSuccess || cudaMalloc(&nc, ccap * sizeof(unsigned)) != cudaSuccess ||
+      cudaMemset(nc, 0, ccap * sizeof(unsigned)) != cudaSuccess) {
+    (void)cudaGetLastError();
+    if (nws) cudaFree(nws);
+    return false;
+  }
+  if (e) {  // grow: the old buffers may still be in use by queued launches -> leak them (rare)
+    e->ws = nws;
+    e->ws_bytes = want;
+    e->counters = nc;
+    e->counter_cap = ccap;
+  } else {
+    g_splitk.push_back(SplitKScratch{dev, st, nws, want, nc, ccap});
+  }
+  *ws = nws;
+  *counters = nc;
+  return true;
+}
+
+// Mid-M regime (one or two 128-row token blocks): the output has far fewer 128x128 tiles than the
+// chip has SMs and a single CTA ingests only ~55 GB/s (measured: 48 CTAs -> 16 us for a 25 MB
+// weight, whatever M), so K is split until roughly every SM streams (B200_GEMM_SPLITK=0 disables,
+// =n forces n).  At least 4 K blocks per slice, at most 8 slices.
+int splitk_pick(int tiles, int num_kb, int sms) {
+  static int forced = env_int("B200_GEMM_SPLITK", -1);
+  if (forced == 0) return 1;
+  int s = forced > 0 ? forced : sms / (tiles > 0 ? tiles : 1);
+  if (s > 8) s = 8;
+  if (s > num_kb / 4) s = num_kb / 4;
+  if (s < 1) s = 1;
+  while (s > 1 && (s - 1) * ceil_div(num_kb, s) >= num_kb) --s;  // no empty slice
   return s;
 }
 
@@ -217,10 +295,10 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
   int rc;
   if (out_dtype == B200_BF16) {
     rc = big ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm")
-             : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm");
+             : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm", true);
   } else {
     rc = big ? launch_gemm_tn<kKindFp8, 256, 4, __half>(a, lda, b, ldb, ep, st, "fp8_gemm")
-             : launch_gemm_tn<kKindFp8, 128, 6, __half>(a, lda, b, ldb, ep, st, "fp8_gemm");
+             : launch_gemm_tn<kKindFp8, 128, 6, __half>(a, lda, b, ldb, ep, st, "fp8_gemm", true);
   }
   if (rc || !comm) return rc;
   return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);

@@ -25,6 +25,14 @@ struct GemmEpilogueParams {
   int sa_stride, sb_stride;
   const void* bias;     // [N] OutT or null
   int M, N, K;
+  // Split-K (mid-M regime: too few output tiles to occupy the SMs, see launch_gemm_tn): work item
+  // = (tile, k-slice); every item writes its fp32 partial tile to `ws`, the LAST item of a tile to
+  // arrive (atomic ticket in `counters`) sums the `splits` partials in slice order — deterministic —
+  // and runs the normal epilogue.  splits == 1: plain path, ws/counters unused.
+  int splits = 1;
+  int kb_per_split = 0;
+  float* ws = nullptr;          // [tiles * splits][BLOCK_N][128] fp32
+  unsigned* counters = nullptr; // [tiles], zero between launches
 };
 
 template <int KIND>
@@ -62,6 +70,10 @@ struct GemmCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
+__device__ __forceinline__ void named_bar_sync_gemm(int id, int threads) {
+  asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(threads) : "memory");
+}
+
 template <typename OutT>
 __device__ __forceinline__ uint32_t pack_out2(float a, float b);
 template <>
@@ -90,6 +102,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
       smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  volatile unsigned* ticket = reinterpret_cast<volatile unsigned*>(tmem_slot_ptr + 1);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -98,6 +111,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const int n_blocks = ceil_div(ep.N, BLOCK_N);
   const int num_tiles = m_blocks * n_blocks;
   const int num_kb = ceil_div(ep.K, C::BLOCK_K);
+  const int S = ep.splits;
+  const int num_items = num_tiles * S;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmap_a);
@@ -128,9 +143,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int tile = item / S, ks = item - tile * S;
         const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
+        const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(empty_bar(stage), phase ^ 1u);
           tc::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
@@ -152,13 +170,16 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
+        const int ks = item % S;
+        const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
+        const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
         const int acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1u;
         tc::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);  // epilogue drained this accumulator
         tc::tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(full_bar(stage), phase);
           tc::tc_fence_after();
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
@@ -168,9 +189,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const uint64_t adesc = tc::make_smem_desc_sw128(sa + k * C::UMMA_K_BYTES, 1024, 16);
             const uint64_t bdesc = tc::make_smem_desc_sw128(sb + k * C::UMMA_K_BYTES, 1024, 16);
             if (KIND == kKindFp8)
-              tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
             else
-              tc::mma_f16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              tc::mma_f16(tmem_d, adesc, bdesc, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
           }
           tc::mma_commit(empty_bar(stage));  // smem slot free once these MMAs have read it
           if (++stage == STAGES) {
@@ -187,7 +208,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     OutT* out = static_cast<OutT*>(ep.out);
     const OutT* bias = static_cast<const OutT*>(ep.bias);
     int local = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
+      const int tile = item / S, ks = item - tile * S;
       const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1u;
@@ -198,13 +220,55 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const float sa = (ep.sa && row_ok) ? __ldg(ep.sa + static_cast<int64_t>(row) * ep.sa_stride)
                                          : 1.0f;
       OutT* orow = out + static_cast<int64_t>(row) * ep.ldc;
+      bool reduce_here = false;
+      const float* ws_tile = nullptr;
+      if (S > 1) {
+        // 1. park this k-slice's fp32 partial: ws[item][col][row-in-tile] (a warp stores 128 B)
+        float* wp = ep.ws + static_cast<int64_t>(item) * (BLOCK_N * 128) + quarter * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+          uint32_t r[32];
+          tc::tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N +
+                            c * 32, r);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) __stcg(wp + (c * 32 + j) * 128, __uint_as_float(r[j]));
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(tempty_bar(acc));  // accumulator is free for the next item
+        // 2. ticket: the last slice of this tile to arrive reduces
+        __threadfence();
+        named_bar_sync_gemm(1, 128);
+        if (threadIdx.x == 64) {  // first epilogue thread
+          const unsigned prev = atomicAdd(ep.counters + tile, 1u);
+          *ticket = prev;
+        }
+        named_bar_sync_gemm(1, 128);
+        reduce_here = (*ticket == static_cast<unsigned>(S - 1));
+        named_bar_sync_gemm(1, 128);  // ticket may be overwritten by the next item
+        if (!reduce_here) continue;
+        __threadfence();
+        ws_tile = ep.ws + static_cast<int64_t>(tile) * S * (BLOCK_N * 128) + quarter * 32 + lane;
+        (void)ks;
+      }
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
-        const uint32_t taddr =
-            tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + c * 32;
-        tc::tmem_ld32(taddr, r);
-        tc::tmem_ld_wait();
+        if (S > 1) {  // sum the k-slices in slice order (deterministic)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float sum = 0.f;
+            for (int q = 0; q < S; ++q)
+              sum += __ldcg(ws_tile + (static_cast<int64_t>(q) * BLOCK_N + c * 32 + j) * 128);
+            r[j] = __float_as_uint(sum);
+          }
+        } else {
+          const uint32_t taddr =
+              tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + c * 32;
+          tc::tmem_ld32(taddr, r);
+          tc::tmem_ld_wait();
+        }
         const int col0 = n_blk * BLOCK_N + c * 32;
         if (row_ok && col0 < ep.N) {
           if (col0 + 32 <= ep.N && (ep.ldc & 7) == 0) {
@@ -242,9 +306,14 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           }
         }
       }
-      tc::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
+      if (S > 1) {
+        named_bar_sync_gemm(1, 128);
+        if (threadIdx.x == 64) ep.counters[tile] = 0u;  // ready for the next launch
+      } else {
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
+      }
     }
   }
 
@@ -253,11 +322,21 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if (warp == 1) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
 }
 
+// Split-K scratch (fp32 partial tiles + per-tile tickets), one per (device, stream), owned by the
+// library and grown on demand.  Returns false when it cannot be provided (allocation failed, or a
+// larger buffer would have to be allocated while the stream is being captured) — the caller then
+// launches without split-K.
+bool splitk_workspace(cudaStream_t st, size_t ws_bytes, int tiles, float** ws, unsigned** counters);
+// Split factor for `tiles` output tiles of `num_kb` K blocks on `sms` SMs (1 = no split).
+int splitk_pick(int tiles, int num_kb, int sms);
+
 // Host launcher: builds the two TMA descriptors and launches one CTA per SM (or per tile).
 template <int KIND, int BLOCK_N, int STAGES, typename OutT>
 int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
-                   const GemmEpilogueParams& ep, cudaStream_t st, const char* timer_name) {
+                   const GemmEpilogueParams& ep_in, cudaStream_t st, const char* timer_name,
+                   bool allow_split = false) {
   using C = GemmCfg<KIND, BLOCK_N, STAGES>;
+  GemmEpilogueParams ep = ep_in;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d(&ta, a, ep.M, ep.K, lda * C::ELT, C::BLOCK_M, C::BLOCK_K, C::ELT, false);
   if (rc) return rc;
@@ -272,7 +351,18 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
   }
   const int tiles = ceil_div(ep.M, C::BLOCK_M) * ceil_div(ep.N, BLOCK_N);
   const int sms = device_sm_count();
-  const int grid = tiles < sms ? tiles : sms;
+  ep.splits = 1;
+  if (allow_split) {
+    const int num_kb = ceil_div(ep.K, C::BLOCK_K);
+    const int S = splitk_pick(tiles, num_kb, sms);
+    if (S > 1 && splitk_workspace(st, static_cast<size_t>(tiles) * S * BLOCK_N * 128 * 4, tiles,
+                                  &ep.ws, &ep.counters)) {
+      ep.splits = S;
+      ep.kb_per_split = ceil_div(num_kb, S);
+    }
+  }
+  const int items = tiles * ep.splits;
+  const int grid = items < sms ? items : sms;
   {
     ScopedKernelTimer timer(timer_name, st);
     B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, 1, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));

@@ -145,11 +145,24 @@ class B200AttnBackend(AttentionBackend):
         v_cache = pool.get_value_buffer(layer.layer_id)
         if k.dtype != k_cache.dtype:
             # quantised KV cache (FP8): scaling/cast order is owned by the pool
-            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, layer.k_scale,
-                               layer.v_scale)
+            ks, vs = self._kv_scales(layer)
+            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, ks, vs)
         else:
             kv_write(k, v, k_cache, v_cache, forward_batch.out_cache_loc)
         return k_cache, v_cache
+
+    @staticmethod
+    def _kv_scales(layer):
+        """(k_scale, v_scale) as host floats, or (None, None) when the layer has none
+        (FlashInfer passes layer.k_scale/v_scale, flashinfer_backend.py:427,499; the float copies
+        are radix_attention.py:74-75)."""
+        ks = getattr(layer, "k_scale_float", None)
+        vs = getattr(layer, "v_scale_float", None)
+        if ks is None and layer.k_scale is not None:
+            ks = float(layer.k_scale)
+        if vs is None and layer.v_scale is not None:
+            vs = float(layer.v_scale)
+        return ks, vs
 
     def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
         hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
@@ -167,13 +180,26 @@ class B200AttnBackend(AttentionBackend):
             v_cache = pool.get_value_buffer(layer.layer_id)
         if bs == 0:
             return o
-        if k_cache.dtype != q.dtype:
-            raise _lib.B200Error(
-                f"B200AttnBackend.forward_decode: KV cache dtype {k_cache.dtype} != q dtype "
-                f"{q.dtype} (FP8 KV cache is a later row of the scope table)")
         md = self.forward_metadata
         req_to_token = forward_batch.req_to_token_pool.req_to_token
         ws = md.workspace
+        if k_cache.dtype == torch.float8_e4m3fn:
+            ks, vs = self._kv_scales(layer)
+            rc = self.lib.b200_attn_decode_fp8kv(
+                q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                k_cache.stride(0), o.data_ptr(), o.stride(0), req_to_token.data_ptr(),
+                req_to_token.stride(0), _as_i64(forward_batch.req_pool_indices).data_ptr(),
+                _as_i64(forward_batch.seq_lens).data_ptr(), bs, hq, hkv, d, dv,
+                float(layer.scaling), float(layer.logit_cap or 0.0),
+                1.0 if ks is None else ks, 1.0 if vs is None else vs, _lib.dtype_code(q.dtype),
+                _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits,
+                _lib.current_stream())
+            _lib.check(rc, "b200_attn_decode_fp8kv")
+            return o
+        if k_cache.dtype != q.dtype:
+            raise _lib.B200Error(
+                f"B200AttnBackend.forward_decode: KV cache dtype {k_cache.dtype} != q dtype "
+                f"{q.dtype} (supported pools: the activation dtype or float8_e4m3fn)")
         rc = self.lib.b200_attn_decode(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
             o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),

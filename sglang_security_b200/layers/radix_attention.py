@@ -32,6 +32,8 @@ class RadixAttention(nn.Module):
         self.attn_type = attn_type
         self.k_scale = None
         self.v_scale = None
+        self.k_scale_float = None   # host copies (radix_attention.py:74-75): no .item() per step
+        self.v_scale_float = None
 
     def forward(self, q, k, v, forward_batch, save_kv_cache: bool = True, **kwargs):
         if k is not None:

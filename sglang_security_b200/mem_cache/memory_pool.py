@@ -125,16 +125,52 @@ class MHATokenToKVPool:
 
     def set_kv_buffer(self, layer, loc: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor,
                       k_scale: Optional[float] = None, v_scale: Optional[float] = None):
-        if cache_k.dtype != self.dtype:
-            # same order of operations as the reference: in-place divide, then cast
-            if k_scale is not None:
-                cache_k.div_(k_scale)
-            if v_scale is not None:
-                cache_v.div_(v_scale)
-            cache_k = cache_k.to(self.dtype)
-            cache_v = cache_v.to(self.dtype)
         idx = layer.layer_id - self.start_layer
+        if cache_k.dtype != self.dtype:
+            # FP8 pool: divide by the scale, cast and scatter in ONE kernel, bit-exact with the
+            # reference's `div_` -> `.to(fp8)` -> index_put (memory_pool.py:390-412)
+            if self.dtype != torch.float8_e4m3fn:
+                raise _lib.B200Error(f"KV cache dtype {self.dtype} is not supported "
+                                     "(bf16/f16 or float8_e4m3fn)")
+            if (k_scale is None) != (v_scale is None):
+                raise _lib.B200Error("set_kv_buffer: k_scale and v_scale must be given together")
+            kv_write_fp8(cache_k, cache_v, self.k_buffer[idx], self.v_buffer[idx], loc,
+                         k_scale, v_scale)
+            return
         kv_write(cache_k, cache_v, self.k_buffer[idx], self.v_buffer[idx], loc)
+
+
+def _scale_value(s) -> float:
+    return float(s) if s is not None else 1.0
+
+
+def kv_write_fp8(k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                 loc: torch.Tensor, k_scale=None, v_scale=None) -> None:
+    """Quantising scatter into an e4m3 pool stored as bytes (b200_kv_write_fp8).  Scales are host
+    floats (RadixAttention.k_scale_float / v_scale_float) so no device sync is needed."""
+    if not k.is_cuda:
+        raise _lib.B200Error("kv_write_fp8: tensors must live on a CUDA device (no CPU path)")
+    num_tokens = loc.numel()
+    if num_tokens == 0:
+        return
+    k = k.reshape(num_tokens, -1) if k.dim() != 2 else k
+    v = v.reshape(num_tokens, -1) if v.dim() != 2 else v
+    if k.stride(-1) != 1:
+        k = k.contiguous()
+    if v.stride(-1) != 1:
+        v = v.contiguous()
+    if loc.dtype != torch.int64:
+        loc = loc.to(torch.int64)
+    row = k.shape[1]
+    if v.shape[1] != row or k_cache[0].numel() != row or v_cache[0].numel() != row \
+            or k_cache.element_size() != 1 or not k_cache.is_contiguous():
+        raise _lib.B200Error("kv_write_fp8: row does not match the cache row layout")
+    rc = _lib.load().b200_kv_write_fp8(
+        k.data_ptr(), v.data_ptr(), k.stride(0), v.stride(0), k_cache.data_ptr(),
+        v_cache.data_ptr(), loc.data_ptr(), num_tokens, row, _scale_value(k_scale),
+        _scale_value(v_scale), 0 if k_scale is None else 1, _lib.dtype_code(k.dtype),
+        _lib.current_stream())
+    _lib.check(rc, "b200_kv_write_fp8")
 
 
 def kv_write(k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_fp8_gpu.py tests/test_fp8_kv_gpu.py -x -q > gpurun_out/pytest_fp8.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_fp8.log | cut -c1-300
+B200_FP8KV_STAGES=3 timeout 600 python tools/sweep_decode.py --tune --kv-dtype fp8 --out gpurun_out/sweep_decode_fp8kv_st3.json 2>&1 | head -2 | cut -c1-300
+B200_FP8KV_STAGES=3 timeout 300 python -m pytest tests/test_fp8_kv_gpu.py -x -q 2>&1 | tail -2
+timeout 900 python tools/bench_gemm_decode.py --ms 48,64,96,128,192,256 --kinds rowcol,torch_rowwise --variants auto,big --out gpurun_out/bench_gemm_midm_splitk.json > gpurun_out/bench_gemm_midm_splitk.log 2>&1; echo "midm rc=$?"; cut -c1-330 gpurun_out/bench_gemm_midm_splitk.log

@@ -22,14 +22,20 @@ from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool, ReqToTo
 from sglang_security_b200.model_executor.forward_batch_info import ForwardBatch, ForwardMode
 
 
-def run_point(bs, ctx, hq, hkv, d, layers, slots_mode, splits, iters, ragged=False):
+def run_point(bs, ctx, hq, hkv, d, layers, slots_mode, splits, iters, ragged=False, kv_dtype="bf16"):
     dev = torch.device("cuda")
     size = bs * ctx
     rtp = ReqToTokenPool(bs + 1, ctx + 4, dev)
-    kvp = MHATokenToKVPool(size, 1, torch.bfloat16, hkv, d, layers, dev)
+    fp8 = kv_dtype == "fp8"
+    kvp = MHATokenToKVPool(size, 1, torch.float8_e4m3fn if fp8 else torch.bfloat16, hkv, d, layers, dev)
     for l in range(layers):
-        kvp.k_buffer[l].normal_()
-        kvp.v_buffer[l].normal_()
+        if fp8:  # random e4m3 bytes, NaN patterns (0x7f / 0xff) remapped
+            for buf in (kvp.k_buffer[l], kvp.v_buffer[l]):
+                buf.random_(0, 256)
+                buf[(buf & 0x7f) == 0x7f] = 0x38
+        else:
+            kvp.k_buffer[l].normal_()
+            kvp.v_buffer[l].normal_()
     g = torch.Generator().manual_seed(0)
     slots = (torch.randperm(size, generator=g) + 1) if slots_mode == "random" else torch.arange(1, size + 1)
     rtp.req_to_token[:bs, :ctx] = slots.view(bs, ctx).to(torch.int32).to(dev)
@@ -58,12 +64,12 @@ def run_point(bs, ctx, hq, hkv, d, layers, slots_mode, splits, iters, ragged=Fal
             attn[l](q[l], None, None, fb, save_kv_cache=False)
     torch.cuda.synchronize()
     _lib.timing_enable(False)
-    n, ms = _lib.timing_read("attn_decode_split")
+    n, ms = _lib.timing_read("attn_decode_fp8kv" if fp8 else "attn_decode_split")
     nm, msm = _lib.timing_read("attn_merge")
     tokens = int(lens.sum())
-    bytes_ = tokens * hkv * 2 * d * 2 + bs * hq * d * 2 * 2 + tokens * 4
+    bytes_ = tokens * hkv * 2 * d * (1 if fp8 else 2) + bs * hq * d * 2 * 2 + tokens * 4
     us = ms / n * 1e3
-    return dict(bs=bs, ctx=ctx, hq=hq, hkv=hkv, d=d, slots=slots_mode, ragged=ragged,
+    return dict(bs=bs, ctx=ctx, hq=hq, hkv=hkv, d=d, slots=slots_mode, ragged=ragged, kv_dtype=kv_dtype,
                 splits=backend.forward_metadata.num_splits, split_us=round(us, 2),
                 merge_us=round(msm / nm * 1e3, 2) if nm else 0.0,
                 gbs=round(bytes_ / (us * 1e-6) / 1e9, 1))
@@ -73,6 +79,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--tune", action="store_true", help="cfg-2 point only, a few split counts")
+    ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"])
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep_decode.json"))
     args = ap.parse_args()
     peak = 6541.5
@@ -103,7 +110,7 @@ def main():
             dict(bs=16, ctx=16384, hq=32, hkv=8, d=128, layers=4, slots_mode="random", splits=0),
         ]
     for p in points:
-        r = run_point(iters=5, **p)
+        r = run_point(iters=5, kv_dtype=args.kv_dtype, **p)
         r["frac_of_measured_peak"] = round(r["gbs"] / peak, 3)
         rows.append(r)
         print(json.dumps(r), flush=True)
