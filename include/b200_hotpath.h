@@ -149,6 +149,28 @@ int b200_attn_extend(const void* q, int64_t q_stride, const void* k_cache, const
                      int D, int Dv, float scale, float logit_cap, int causal, int dtype,
                      void* stream);
 
+/* Same kernel with an output multiplier: extend over an FP8 KV pool runs on an exact 16-bit copy
+ * of the requests' rows (b200_kv_dequant_gather) with scale * k_scale and out_scale = v_scale.    */
+int b200_attn_extend_scaled(const void* q, int64_t q_stride, const void* k_cache,
+                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                            const int32_t* req_to_token, int64_t req_to_token_stride,
+                            const int64_t* req_pool_indices, const int64_t* seq_lens,
+                            const int32_t* extend_prefix_lens, const int32_t* extend_seq_lens,
+                            const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq,
+                            int Hkv, int D, int Dv, float scale, float logit_cap, float out_scale,
+                            int causal, int dtype, void* stream);
+/* FP8 (e4m3) pool -> dense 16-bit rows for the extend kernel (prefill is compute-bound; the extra
+ * pass costs 3 bytes/element once per layer): for request b and t < seq_lens[b]
+ *   k_out[kv_indptr[b] + t, :] = exact(k_cache[slot(b,t), :]),  dense_rtt[b, t] = kv_indptr[b] + t
+ * k_cache/v_cache [slots, row_elems] bytes; k_out/v_out [sum seq_lens, row_elems] bf16/f16;
+ * kv_indptr int32 [bs+1] exclusive prefix sum of seq_lens; max_len >= max_b seq_lens[b].          */
+int b200_kv_dequant_gather(const void* k_cache, const void* v_cache, int row_elems,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens,
+                           const int32_t* kv_indptr, void* k_out, void* v_out, int32_t* dense_rtt,
+                           int64_t dense_rtt_stride, int bs, int64_t max_len, int dtype,
+                           void* stream);
+
 /* ---- FP8 activation quantisation ----------------------------------------- */
 /* Per-token dynamic (static_scale == NULL): scales[m] = absmax(x[m,:]) / 448, q = sat(x * (1/scale))
  *   replaces sgl_per_token_quant_fp8 (sgl-kernel/csrc/gemm/per_token_quant_fp8.cu:9-106).
@@ -310,6 +332,38 @@ int b200_fp8_gemm_block128_ar(void* comm, const void* a, int64_t lda, const void
                               const float* as, int64_t as_row_stride, int64_t as_col_stride,
                               const float* bs, int64_t bs_row_stride, const void* bias, void* out,
                               int64_t ldc, int M, int N, int K, int out_dtype, void* stream);
+
+/* ---- scheduler-side index kernels (page_size >= 1) --------------------------------------------- */
+/* int64/int32 index arithmetic, bit-exact with the reference's Triton kernels.  All tensors device.
+ * write_req_to_token_pool_triton (managers/schedule_batch.py:1789-1823, called :1272-1283):
+ *   req_to_token[req_pool_indices[b], pre_lens[b] : seq_lens[b]] =
+ *       out_cache_loc[sum(extend_lens[:b]) : sum(extend_lens[:b]) + seq_lens[b] - pre_lens[b]]    */
+int b200_write_req_to_token(int32_t* req_to_token, int64_t req_to_token_stride,
+                            const int64_t* req_pool_indices, const int64_t* pre_lens,
+                            const int64_t* seq_lens, const int64_t* extend_lens,
+                            const int64_t* out_cache_loc, int bs, void* stream);
+/* get_last_loc (managers/schedule_batch.py:1826-1893):
+ *   result[i] = prefix_lens[i] > 0 ? req_to_token[req_pool_indices[i], prefix_lens[i] - 1] : -1   */
+int b200_get_last_loc(const int32_t* req_to_token, int64_t req_to_token_stride,
+                      const int64_t* req_pool_indices, const int64_t* prefix_lens, int64_t* result,
+                      int n, void* stream);
+/* alloc_extend_kernel / alloc_decode_kernel of PagedTokenToKVPoolAllocator
+ * (mem_cache/paged_allocator.py:29-155): token slot ids of the new tokens of every request — first
+ * the rest of the partially filled last page (last_loc + 1 ...), then whole pages taken in order
+ * from free_pages, then the head of one more page.  *ret_values = (new pages << 32) | new tokens
+ * (extend) or the number of new pages (decode), which the host uses to pop free_pages.           */
+int b200_alloc_extend(const int64_t* pre_lens, const int64_t* seq_lens, const int64_t* last_loc,
+                      const int64_t* free_pages, int64_t* out_indices, int64_t* ret_values, int bs,
+                      int page_size, void* stream);
+int b200_alloc_decode(const int64_t* seq_lens, const int64_t* last_loc, const int64_t* free_pages,
+                      int64_t* out_indices, int64_t* ret_values, int bs, int page_size,
+                      void* stream);
+/* compute_position_kernel (model_executor/forward_batch_info.py:639-692): positions of the new
+ * tokens (prefix_len + i) and extend_start_loc = exclusive cumsum of extend_seq_lens.
+ * extend_prefix_lens may be NULL (no prefix).                                                     */
+int b200_compute_position(int64_t* positions, int32_t* extend_start_loc,
+                          const int32_t* extend_prefix_lens, const int32_t* extend_seq_lens, int bs,
+                          void* stream);
 
 #ifdef __cplusplus
 }

@@ -58,8 +58,9 @@ def decode_attention_oracle(q, k_cache, v_cache, req_to_token, req_pool_indices,
 
 def extend_attention_oracle(q, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens,
                             extend_prefix_lens, extend_seq_lens, scale, causal=True,
-                            logit_cap=0.0):
-    """q [T, Hq, D] (new tokens of all requests, concatenated) -> o [T, Hq, Dv]."""
+                            logit_cap=0.0, k_scale=1.0, v_scale=1.0):
+    """q [T, Hq, D] (new tokens of all requests, concatenated) -> o [T, Hq, Dv].
+    k_scale / v_scale: de-quantisation scales of an FP8 pool (see decode_attention_oracle)."""
     t, hq, _ = q.shape
     dv = v_cache.shape[-1]
     o = torch.empty((t, hq, dv), dtype=q.dtype)
@@ -67,8 +68,8 @@ def extend_attention_oracle(q, k_cache, v_cache, req_to_token, req_pool_indices,
     for b in range(len(seq_lens)):
         n, pre, ext = int(seq_lens[b]), int(extend_prefix_lens[b]), int(extend_seq_lens[b])
         tok = req_to_token[int(req_pool_indices[b]), :n].long()
-        k = k_cache[tok].float().transpose(0, 1)
-        v = v_cache[tok].float().transpose(0, 1)
+        k = k_cache[tok].float().transpose(0, 1) * k_scale
+        v = v_cache[tok].float().transpose(0, 1) * v_scale
         qb = q[start:start + ext].float().transpose(0, 1)  # [Hq, ext, D]
         out = _attend(qb, k, v, scale, pre if causal else None, logit_cap)
         o[start:start + ext] = out.transpose(0, 1).to(q.dtype)

@@ -32,6 +32,21 @@ _SIGNATURES = {
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_int, c_int, c_float, c_float, c_float, c_float,
                                        c_int, c_void_p, c_size_t, c_int, c_void_p]),
+    "b200_kv_dequant_gather": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                       c_int64, c_int, c_void_p]),
+    "b200_attn_extend_scaled": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        c_float, c_float, c_float, c_int, c_int, c_void_p]),
+    "b200_write_req_to_token": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_int, c_void_p]),
+    "b200_get_last_loc": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "b200_alloc_extend": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                  c_int, c_void_p]),
+    "b200_alloc_decode": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                  c_void_p]),
+    "b200_compute_position": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "b200_kv_indices": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_int, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

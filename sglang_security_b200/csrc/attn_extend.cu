@@ -43,6 +43,7 @@ struct ExtendParams {
   int Hq, Hkv, group, pack, head_tiles;
   float qk_scale;                // scale*log2e, or scale when capped
   float logit_cap;
+  float out_scale;               // output multiplier (v_scale of an FP8 KV pool; 1 otherwise)
   int causal;
 };
 
@@ -324,7 +325,7 @@ attn_extend_kernel(const ExtendParams p) {
     // ---- epilogue: O / l -> out
     tc::mbar_wait(bar_pv_full, (n_kv - 1) & 1u);
     tc::tc_fence_after();
-    const float inv_l = l > 0.f ? 1.f / l : 0.f;
+    const float inv_l = l > 0.f ? p.out_scale / l : 0.f;
     T* orow = static_cast<T*>(p.o) + (q_row0 + (row_ok ? tok : 0)) * p.o_stride +
               static_cast<int64_t>(head_base + r % p.pack) * D;
 #pragma unroll 1
@@ -391,6 +392,21 @@ int b200_attn_extend(const void* q, int64_t q_stride, const void* k_cache, const
                      const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq, int Hkv,
                      int D, int Dv, float scale, float logit_cap, int causal, int dtype,
                      void* stream) {
+  return b200_attn_extend_scaled(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride,
+                                 req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                                 extend_prefix_lens, extend_seq_lens, extend_start_loc, bs,
+                                 max_extend_len, Hq, Hkv, D, Dv, scale, logit_cap, 1.0f, causal,
+                                 dtype, stream);
+}
+
+int b200_attn_extend_scaled(const void* q, int64_t q_stride, const void* k_cache,
+                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                            const int32_t* req_to_token, int64_t req_to_token_stride,
+                            const int64_t* req_pool_indices, const int64_t* seq_lens,
+                            const int32_t* extend_prefix_lens, const int32_t* extend_seq_lens,
+                            const int32_t* extend_start_loc, int bs, int max_extend_len, int Hq,
+                            int Hkv, int D, int Dv, float scale, float logit_cap, float out_scale,
+                            int causal, int dtype, void* stream) {
   using namespace b200;
   if (bs == 0 || max_extend_len == 0) return 0;
   B200_REQUIRE(q && k_cache && v_cache && o && req_to_token && req_pool_indices && seq_lens &&
@@ -429,6 +445,7 @@ int b200_attn_extend(const void* q, int64_t q_stride, const void* k_cache, const
   p.pack = pack;
   p.head_tiles = p.group / pack;
   p.logit_cap = logit_cap;
+  p.out_scale = out_scale;
   p.qk_scale = logit_cap > 0.f ? scale : scale * 1.4426950408889634f;
   p.causal = causal;
   B200_REQUIRE(bs <= 65535 && Hkv * p.head_tiles <= 65535, "b200_attn_extend: grid too large");

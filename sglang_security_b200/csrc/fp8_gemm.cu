@@ -111,67 +111,6 @@ int smallm_pick_splits(int n_tiles, int num_kb) {
   return s;
 }
 
-// ---- split-K scratch for the big-tile kernel ------------------------------------------------------
-struct SplitKScratch {
-  int dev;
-  cudaStream_t st;
-  float* ws;
-  size_t ws_bytes;
-  unsigned* counters;
-  int counter_cap;
-};
-static std::mutex g_splitk_mu;
-static std::vector<SplitKScratch> g_splitk;
-
-bool splitk_workspace(cudaStream_t st, size_t ws_bytes, int tiles, float** ws, unsigned** counters) {
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  std::lock_guard<std::mutex> lk(g_splitk_mu);
-  SplitKScratch* e = nullptr;
-  for (auto& x : g_splitk)
-    if (x.dev == dev && x.st == st) e = &x;
-  if (e && e->ws_bytes >= ws_bytes && e->counter_cap >= tiles) {
-    *ws = e->ws;
-    *counters = e->counters;
-    return true;
-  }
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
-    // a captured stream is usually a side stream: share the scratch of any stream of this device
-    // that is large enough (launches on different streams of one process are ordered by the
-    // framework around graph capture), never allocate during capture
-    for (auto& x : g_splitk)
-      if (x.dev == dev && x.ws_bytes >= ws_bytes && x.counter_cap >= tiles) {
-        *ws = x.ws;
-        *counters = x.counters;
-        return true;
-      }
-    (void)cudaGetLastError();
-    return false;
-  }
-  const size_t want = ws_bytes < (static_cast<size_t>(32) << 20) ? (static_cast<size_t>(32) << 20) : ws_bytes;
-  const int ccap = tiles < 1024 ? 1024 : tiles;
-  float* nws = nullptr;
-  unsigned* nc = nullptr;
-  if (cudaMalloc(&nws, want) != cudaSuccess || cudaMalloc(&nc, ccap * sizeof(unsigned)) != cudaSuccess ||
-      cudaMemset(nc, 0, ccap * sizeof(unsigned)) != cudaSuccess) {
-    (void)cudaGetLastError();
-    if (nws) cudaFree(nws);
-    return false;
-  }
-  if (e) {  // grow: the old buffers may still be in use by queued launches -> leak them (rare)
-    e->ws = nws;
-    e->ws_bytes = want;
-    e->counters = nc;
-    e->counter_cap = ccap;
-  } else {
-    g_splitk.push_back(SplitKScratch{dev, st, nws, want, nc, ccap});
-  }
-  *ws = nws;
-  *counters = nc;
-  return true;
-}
-
 // Mid-M regime (one or two 128-row token blocks): the output has far fewer 128x128 tiles than the
 // chip has SMs and a single CTA ingests only ~55 GB/s (measured: 48 CTAs -> 16 us for a 25 MB
 // weight, whatever M), so K is split until roughly every SM streams (B200_GEMM_SPLITK=0 disables,
@@ -265,11 +204,11 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
   ep.K = K;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // Decode regime: weight streaming, swap-AB + cluster split-K.  Measured crossover against the
-  // big-tile kernel (profiles/r01_gemm_decode.json): always for M <= 64; for 64 < M <= 128 only when
-  // K is long (down_proj) — the per-SM TMA row rate (128 weight rows + MT token rows per K block)
-  // makes MT = 128 cost as much as a full 128x128 tile.
+  // big-tile kernel with cluster split-K (profiles/r01_bench_gemm_midm_splitk.json): the swap-AB
+  // kernel wins up to M = 32; from M = 33 the 128x128 tile split over K is faster on every
+  // Llama-3.1-8B shape (10.8 vs 15.4-20.6 us at N = K = 4096, 17.2 vs 21.7-27 us at K = 14336).
   const bool fuse_ar = comm_can_fuse(comm, M, N);
-  if (fuse_ar || (M <= smallm_max_m() && (M <= 64 || K >= 8192 || smallm_forced()))) {
+  if (fuse_ar || (M <= smallm_max_m() && (M <= 32 || smallm_forced()))) {
     SmallMParams sp = {};
     if (fuse_ar) {
       sp.use_comm = 1;

@@ -25,14 +25,14 @@ struct GemmEpilogueParams {
   int sa_stride, sb_stride;
   const void* bias;     // [N] OutT or null
   int M, N, K;
-  // Split-K (mid-M regime: too few output tiles to occupy the SMs, see launch_gemm_tn): work item
-  // = (tile, k-slice); every item writes its fp32 partial tile to `ws`, the LAST item of a tile to
-  // arrive (atomic ticket in `counters`) sums the `splits` partials in slice order — deterministic —
-  // and runs the normal epilogue.  splits == 1: plain path, ws/counters unused.
+  // Split-K (mid-M regime: too few output tiles to occupy the SMs, see launch_gemm_tn): the
+  // kernel is launched as thread-block clusters of `splits` CTAs, cluster rank = k-slice of ONE
+  // output tile.  Every CTA parks its fp32 partial tile in its own (now idle) pipeline ring, then
+  // rank r sums the `splits` partials of ITS share of the columns over distributed shared memory
+  // in rank order — deterministic, no global workspace, no atomics — and runs the normal epilogue
+  // on that share.  splits == 1: plain persistent path.
   int splits = 1;
   int kb_per_split = 0;
-  float* ws = nullptr;          // [tiles * splits][BLOCK_N][128] fp32
-  unsigned* counters = nullptr; // [tiles], zero between launches
 };
 
 template <int KIND>
@@ -74,6 +74,32 @@ __device__ __forceinline__ void named_bar_sync_gemm(int id, int threads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(threads) : "memory");
 }
 
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n"
+               "barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+
+__device__ __forceinline__ float ld_cluster_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];\n" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+
 template <typename OutT>
 __device__ __forceinline__ uint32_t pack_out2(float a, float b);
 template <>
@@ -102,7 +128,6 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
       smem_raw + (tmem_slot - smem_u32(smem_raw)));
-  volatile unsigned* ticket = reinterpret_cast<volatile unsigned*>(tmem_slot_ptr + 1);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -220,11 +245,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const float sa = (ep.sa && row_ok) ? __ldg(ep.sa + static_cast<int64_t>(row) * ep.sa_stride)
                                          : 1.0f;
       OutT* orow = out + static_cast<int64_t>(row) * ep.ldc;
-      bool reduce_here = false;
-      const float* ws_tile = nullptr;
       if (S > 1) {
-        // 1. park this k-slice's fp32 partial: ws[item][col][row-in-tile] (a warp stores 128 B)
-        float* wp = ep.ws + static_cast<int64_t>(item) * (BLOCK_N * 128) + quarter * 32 + lane;
+        // 1. park this k-slice's fp32 partial in the idle ring: part[col][row] (conflict-free)
+        const uint32_t part = smem_base + (quarter * 32 + lane) * 4;
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 32; ++c) {
           uint32_t r[32];
@@ -232,43 +255,71 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             c * 32, r);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) __stcg(wp + (c * 32 + j) * 128, __uint_as_float(r[j]));
+          for (int j = 0; j < 32; ++j)
+            asm volatile("st.shared.b32 [%0], %1;\n" ::"r"(part + (c * 32 + j) * 512), "r"(r[j])
+                         : "memory");
         }
         tc::tc_fence_before();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(tempty_bar(acc));  // accumulator is free for the next item
-        // 2. ticket: the last slice of this tile to arrive reduces
-        __threadfence();
-        named_bar_sync_gemm(1, 128);
-        if (threadIdx.x == 64) {  // first epilogue thread
-          const unsigned prev = atomicAdd(ep.counters + tile, 1u);
-          *ticket = prev;
+        cluster_sync_all();  // every partial of this tile is in place (all 192 threads arrive)
+        // 2. my share of the columns, in groups of 8: ranks 0..rem-1 take one extra group
+        constexpr int GROUPS = BLOCK_N / 8;
+        const int base_g = GROUPS / S, rem = GROUPS % S;
+        const int my_rank = static_cast<int>(cluster_ctarank());
+        const int g0 = my_rank * base_g + min(my_rank, rem);
+        const int g1 = g0 + base_g + (my_rank < rem ? 1 : 0);
+        for (int g = g0; g < g1; ++g) {
+          float sum[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+          for (int q = 0; q < S; ++q) {  // rank order
+            const uint32_t src = map_to_rank(part + g * 8 * 512, q);
+            float t[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[j] = ld_cluster_f32(src + j * 512);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sum[j] += t[j];
+          }
+          const int col0 = n_blk * BLOCK_N + g * 8;
+          if (row_ok && col0 < ep.N) {
+            if (col0 + 8 <= ep.N && (ep.ldc & 7) == 0) {
+              uint32_t packed[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float s0 = sa, s1 = sa;
+                if (ep.sb) {
+                  s0 *= __ldg(ep.sb + static_cast<int64_t>(col0 + 2 * e) * ep.sb_stride);
+                  s1 *= __ldg(ep.sb + static_cast<int64_t>(col0 + 2 * e + 1) * ep.sb_stride);
+                }
+                const float b0 = bias ? to_float<OutT>(bias[col0 + 2 * e]) : 0.f;
+                const float b1 = bias ? to_float<OutT>(bias[col0 + 2 * e + 1]) : 0.f;
+                packed[e] = pack_out2<OutT>(fmaf(sum[2 * e], s0, b0), fmaf(sum[2 * e + 1], s1, b1));
+              }
+              *reinterpret_cast<uint4*>(orow + col0) =
+                  make_uint4(packed[0], packed[1], packed[2], packed[3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (col0 + j >= ep.N) break;
+                float sc = sa;
+                if (ep.sb) sc *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
+                const float bb = bias ? to_float<OutT>(bias[col0 + j]) : 0.f;
+                orow[col0 + j] = from_float<OutT>(fmaf(sum[j], sc, bb));
+              }
+            }
+          }
         }
-        named_bar_sync_gemm(1, 128);
-        reduce_here = (*ticket == static_cast<unsigned>(S - 1));
-        named_bar_sync_gemm(1, 128);  // ticket may be overwritten by the next item
-        if (!reduce_here) continue;
-        __threadfence();
-        ws_tile = ep.ws + static_cast<int64_t>(tile) * S * (BLOCK_N * 128) + quarter * 32 + lane;
-        (void)ks;
+        __syncwarp();
+        cluster_sync_all();  // peers have finished reading my partial
+        continue;
       }
 #pragma unroll 1
       for (int c = 0; c < BLOCK_N / 32; ++c) {
         uint32_t r[32];
-        if (S > 1) {  // sum the k-slices in slice order (deterministic)
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float sum = 0.f;
-            for (int q = 0; q < S; ++q)
-              sum += __ldcg(ws_tile + (static_cast<int64_t>(q) * BLOCK_N + c * 32 + j) * 128);
-            r[j] = __float_as_uint(sum);
-          }
-        } else {
-          const uint32_t taddr =
-              tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + c * 32;
-          tc::tmem_ld32(taddr, r);
-          tc::tmem_ld_wait();
-        }
+        const uint32_t taddr =
+            tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BLOCK_N + c * 32;
+        tc::tmem_ld32(taddr, r);
+        tc::tmem_ld_wait();
         const int col0 = n_blk * BLOCK_N + c * 32;
         if (row_ok && col0 < ep.N) {
           if (col0 + 32 <= ep.N && (ep.ldc & 7) == 0) {
@@ -306,15 +357,15 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           }
         }
       }
-      if (S > 1) {
-        named_bar_sync_gemm(1, 128);
-        if (threadIdx.x == 64) ep.counters[tile] = 0u;  // ready for the next launch
-      } else {
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
-      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
     }
+  }
+  if (S > 1 && warp < 2) {  // producer / MMA warps take part in the two cluster barriers
+    __syncwarp();
+    cluster_sync_all();
+    cluster_sync_all();
   }
 
   tc::tc_fence_before();
@@ -322,11 +373,6 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if (warp == 1) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
 }
 
-// Split-K scratch (fp32 partial tiles + per-tile tickets), one per (device, stream), owned by the
-// library and grown on demand.  Returns false when it cannot be provided (allocation failed, or a
-// larger buffer would have to be allocated while the stream is being captured) — the caller then
-// launches without split-K.
-bool splitk_workspace(cudaStream_t st, size_t ws_bytes, int tiles, float** ws, unsigned** counters);
 // Split factor for `tiles` output tiles of `num_kb` K blocks on `sms` SMs (1 = no split).
 int splitk_pick(int tiles, int num_kb, int sms);
 
@@ -352,20 +398,46 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
   const int tiles = ceil_div(ep.M, C::BLOCK_M) * ceil_div(ep.N, BLOCK_N);
   const int sms = device_sm_count();
   ep.splits = 1;
-  if (allow_split) {
+  if (allow_split && BLOCK_N * 128 * 4 <= STAGES * C::STAGE_BYTES) {
     const int num_kb = ceil_div(ep.K, C::BLOCK_K);
-    const int S = splitk_pick(tiles, num_kb, sms);
-    if (S > 1 && splitk_workspace(st, static_cast<size_t>(tiles) * S * BLOCK_N * 128 * 4, tiles,
-                                  &ep.ws, &ep.counters)) {
-      ep.splits = S;
-      ep.kb_per_split = ceil_div(num_kb, S);
+    // largest split whose `tiles` clusters are all co-resident (one wave): cluster placement is
+    // per GPC, so e.g. 48 clusters of 3 do not fit although 144 <= 148 SMs (measured: 24 us in two
+    // waves vs 16 us unsplit).  Occupancy answers are cached per split factor.
+    static int max_clusters[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int S = splitk_pick(tiles, num_kb, sms); S > 1; --S) {
+      if ((S - 1) * ceil_div(num_kb, S) >= num_kb) continue;  // would leave an empty slice
+      if (max_clusters[S] == 0) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(S * 8);
+        cfg.blockDim = dim3(C::THREADS);
+        cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = S;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+          (void)cudaGetLastError();
+          n = -1;
+        }
+        max_clusters[S] = n;
+      }
+      if (max_clusters[S] >= tiles) {
+        ep.splits = S;
+        ep.kb_per_split = ceil_div(num_kb, S);
+        break;
+      }
     }
   }
   const int items = tiles * ep.splits;
-  const int grid = items < sms ? items : sms;
+  // split-K: one item per CTA, clusters of `splits` CTAs; else persistent over the tiles
+  const int grid = ep.splits > 1 ? items : (items < sms ? items : sms);
   {
     ScopedKernelTimer timer(timer_name, st);
-    B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, 1, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));
+    B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, ep.splits, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));
   }
   B200_CHECK_LAUNCH("gemm_tn_kernel");
   return 0;

@@ -3,6 +3,8 @@
 // bit-exact with the reference (memory_pool.py:378-412, layers/attention/utils.py:5-41).
 #include "common.cuh"
 
+#include <type_traits>
+
 namespace b200 {
 
 // One thread moves one VEC-byte chunk of one token row of K or V.
@@ -76,6 +78,62 @@ __global__ void kv_write_fp8_kernel(const T* __restrict__ k, const T* __restrict
       hi |= to_e4m3_torch<T>(e[4 + j], scale, has_scale != 0) << (8 * j);
     }
     *reinterpret_cast<uint2*>(dst + slot * row_elems + c * 8) = make_uint2(lo, hi);
+  }
+}
+
+// e4m3 pool -> dense 16-bit rows of one request (exact: every e4m3 value is a bf16 and an f16
+// value), plus the identity page table the extend kernel will index the dense copy with.
+// grid (chunks of tokens, bs); one thread converts 8 bytes of one row.
+template <typename T>
+__global__ void kv_dequant_gather_kernel(const uint8_t* __restrict__ k8, const uint8_t* __restrict__ v8,
+                                         int row_elems, const int32_t* __restrict__ req_to_token,
+                                         int64_t rtt_stride,
+                                         const int64_t* __restrict__ req_pool_indices,
+                                         const int64_t* __restrict__ seq_lens,
+                                         const int32_t* __restrict__ kv_indptr, T* __restrict__ k_out,
+                                         T* __restrict__ v_out, int32_t* __restrict__ dense_rtt,
+                                         int64_t dense_rtt_stride) {
+  griddep_wait();
+  griddep_launch_dependents();
+  const int b = blockIdx.y;
+  const int len = static_cast<int>(seq_lens[b]);
+  const int base = kv_indptr[b];
+  const int32_t* rtt = req_to_token + req_pool_indices[b] * rtt_stride;
+  const int chunks = row_elems / 8;
+  const int64_t total = static_cast<int64_t>(len) * chunks;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i / chunks);
+    const int c = static_cast<int>(i - static_cast<int64_t>(t) * chunks);
+    const int64_t slot = __ldg(rtt + t);
+    if (c == 0) dense_rtt[b * dense_rtt_stride + t] = base + t;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      const uint8_t* src = (which ? v8 : k8) + slot * row_elems + c * 8;
+      T* dst = (which ? v_out : k_out) + static_cast<int64_t>(base + t) * row_elems + c * 8;
+      const uint2 raw = *reinterpret_cast<const uint2*>(src);
+      const uint32_t w[2] = {raw.x, raw.y};
+      uint32_t o[4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t lo, hi;
+        asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
+            "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+            : "=r"(lo), "=r"(hi)
+            : "r"(w[h]));
+        if (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
+          const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&lo));
+          const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+          const __nv_bfloat162 b0 = __floats2bfloat162_rn(f0.x, f0.y);
+          const __nv_bfloat162 b1 = __floats2bfloat162_rn(f1.x, f1.y);
+          lo = *reinterpret_cast<const uint32_t*>(&b0);
+          hi = *reinterpret_cast<const uint32_t*>(&b1);
+        }
+        o[2 * h] = lo;
+        o[2 * h + 1] = hi;
+      }
+      *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
   }
 }
 
@@ -182,6 +240,51 @@ int b200_kv_write_fp8(const void* k, const void* v, int64_t k_token_stride,
                          num_tokens, row_elems, k_scale, v_scale, has_scale);
   B200_CUDA_OK(lerr);
   B200_CHECK_LAUNCH("b200_kv_write_fp8");
+  return 0;
+}
+
+int b200_kv_dequant_gather(const void* k_cache, const void* v_cache, int row_elems,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens,
+                           const int32_t* kv_indptr, void* k_out, void* v_out, int32_t* dense_rtt,
+                           int64_t dense_rtt_stride, int bs, int64_t max_len, int dtype,
+                           void* stream) {
+  using namespace b200;
+  if (bs == 0 || max_len == 0) return 0;
+  B200_REQUIRE(k_cache && v_cache && req_to_token && req_pool_indices && seq_lens && kv_indptr &&
+                   k_out && v_out && dense_rtt,
+               "b200_kv_dequant_gather: null pointer");
+  B200_REQUIRE(row_elems > 0 && row_elems % 8 == 0 && bs > 0 && bs <= 65535,
+               "b200_kv_dequant_gather: bad sizes (row_elems=%d bs=%d)", row_elems, bs);
+  B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, "b200_kv_dequant_gather: dtype %d", dtype);
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(k_cache) & 7u) == 0 &&
+                   (reinterpret_cast<uintptr_t>(v_cache) & 7u) == 0 && aligned16(k_out) &&
+                   aligned16(v_out),
+               "b200_kv_dequant_gather: misaligned pointers");
+  const int64_t per_req = max_len * (row_elems / 8);
+  int64_t bx = (per_req + 255) / 256;
+  const int64_t cap = (148 * 16 + bs - 1) / bs;
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  dim3 grid(static_cast<unsigned>(bx), static_cast<unsigned>(bs));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ScopedKernelTimer timer("kv_dequant_gather", st);
+  cudaError_t lerr;
+  if (dtype == B200_BF16)
+    lerr = launch_kernel(kv_dequant_gather_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, 1,
+                         kPdlOther & 0, static_cast<const uint8_t*>(k_cache),
+                         static_cast<const uint8_t*>(v_cache), row_elems, req_to_token,
+                         req_to_token_stride, req_pool_indices, seq_lens, kv_indptr,
+                         static_cast<__nv_bfloat16*>(k_out), static_cast<__nv_bfloat16*>(v_out),
+                         dense_rtt, dense_rtt_stride);
+  else
+    lerr = launch_kernel(kv_dequant_gather_kernel<__half>, grid, dim3(256), 0, st, 1, kPdlOther & 0,
+                         static_cast<const uint8_t*>(k_cache), static_cast<const uint8_t*>(v_cache),
+                         row_elems, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                         kv_indptr, static_cast<__half*>(k_out), static_cast<__half*>(v_out),
+                         dense_rtt, dense_rtt_stride);
+  B200_CUDA_OK(lerr);
+  B200_CHECK_LAUNCH("b200_kv_dequant_gather");
   return 0;
 }
 

@@ -229,26 +229,59 @@ class B200AttnBackend(AttentionBackend):
         bs = forward_batch.batch_size
         if q.shape[0] == 0 or bs == 0 or md.max_extend_len == 0:
             return o
-        if k_cache.dtype != q.dtype:
-            raise _lib.B200Error(
-                f"B200AttnBackend.forward_extend: KV cache dtype {k_cache.dtype} != q dtype "
-                f"{q.dtype} (FP8 KV cache is a later row of the scope table)")
         attn_type = getattr(layer, "attn_type", None)
         causal = not (layer.is_cross_attention or
                       getattr(attn_type, "value", attn_type) == "encoder_only")
         req_to_token = forward_batch.req_to_token_pool.req_to_token
-        rc = self.lib.b200_attn_extend(
+        req_pool_indices = _as_i64(forward_batch.req_pool_indices)
+        seq_lens = _as_i64(forward_batch.seq_lens)
+        scaling, out_scale = float(layer.scaling), 1.0
+        if k_cache.dtype == torch.float8_e4m3fn:
+            # FP8 pool: the tcgen05 kernel wants 16-bit operands, so the requests' rows are first
+            # copied (exactly) into a dense 16-bit scratch; scales ride on the softmax scale / output
+            k_cache, v_cache, req_to_token, req_pool_indices = self._dequant_for_extend(
+                forward_batch, k_cache, v_cache, req_to_token, req_pool_indices, seq_lens, hkv * d,
+                q.dtype)
+            ks, vs = self._kv_scales(layer)
+            scaling *= 1.0 if ks is None else ks
+            out_scale = 1.0 if vs is None else vs
+        elif k_cache.dtype != q.dtype:
+            raise _lib.B200Error(
+                f"B200AttnBackend.forward_extend: KV cache dtype {k_cache.dtype} != q dtype "
+                f"{q.dtype} (supported pools: the activation dtype or float8_e4m3fn)")
+        rc = self.lib.b200_attn_extend_scaled(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
             o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
-            _as_i64(forward_batch.req_pool_indices).data_ptr(),
-            _as_i64(forward_batch.seq_lens).data_ptr(),
+            req_pool_indices.data_ptr(), seq_lens.data_ptr(),
             forward_batch.extend_prefix_lens.to(torch.int32).data_ptr(),
             forward_batch.extend_seq_lens.to(torch.int32).data_ptr(), md.qo_indptr.data_ptr(), bs,
-            md.max_extend_len, hq, hkv, d, dv, float(layer.scaling),
-            float(layer.logit_cap or 0.0), 1 if causal else 0, _lib.dtype_code(q.dtype),
-            _lib.current_stream())
+            md.max_extend_len, hq, hkv, d, dv, scaling, float(layer.logit_cap or 0.0), out_scale,
+            1 if causal else 0, _lib.dtype_code(q.dtype), _lib.current_stream())
         _lib.check(rc, "b200_attn_extend")
         return o
+
+    def _dequant_for_extend(self, forward_batch, k_cache, v_cache, req_to_token, req_pool_indices,
+                            seq_lens, row_elems, dtype):
+        """-> (k16, v16, dense_req_to_token, dense_req_pool_indices) for an e4m3 pool."""
+        bs = seq_lens.numel()
+        cpu = getattr(forward_batch, "seq_lens_cpu", None)
+        if cpu is not None:
+            total, max_len = int(cpu.sum()), int(cpu.max())
+        else:
+            total, max_len = int(seq_lens.sum().item()), int(seq_lens.max().item())
+        indptr = torch.zeros(bs + 1, dtype=torch.int32, device=seq_lens.device)
+        indptr[1:] = torch.cumsum(seq_lens, dim=0)
+        k16 = torch.empty((total, row_elems), dtype=dtype, device=seq_lens.device)
+        v16 = torch.empty_like(k16)
+        stride = (max_len + 3) // 4 * 4
+        dense_rtt = torch.empty((bs, stride), dtype=torch.int32, device=seq_lens.device)
+        rc = self.lib.b200_kv_dequant_gather(
+            k_cache.data_ptr(), v_cache.data_ptr(), row_elems, req_to_token.data_ptr(),
+            req_to_token.stride(0), req_pool_indices.data_ptr(), seq_lens.data_ptr(),
+            indptr.data_ptr(), k16.data_ptr(), v16.data_ptr(), dense_rtt.data_ptr(), stride, bs,
+            max_len, _lib.dtype_code(dtype), _lib.current_stream())
+        _lib.check(rc, "b200_kv_dequant_gather")
+        return k16, v16, dense_rtt, torch.arange(bs, dtype=torch.int64, device=seq_lens.device)
 
     def support_triton(self):
         return False

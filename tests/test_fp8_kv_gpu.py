@@ -124,3 +124,60 @@ def test_decode_fp8kv_f16_q_and_logit_cap():
     assert torch.equal(kb, kb_ref)
     st = harness.error_stats(o, o_ref)
     assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, st
+
+
+@pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64)])
+@pytest.mark.parametrize("scales", [None, (0.5, 1.25)])
+def test_extend_fp8kv_matches_oracle(hq, hkv, d, scales):
+    """Extend (cached radix prefix + new tokens) over the e4m3 pool: new K/V quantised by the
+    write kernel, attention over the exact 16-bit copy of the rows (b200_kv_dequant_gather)."""
+    import harness
+    from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
+    from sglang_security_b200.model_executor.forward_batch_info import ForwardBatch, ForwardMode
+
+    case = scenarios.make_attention_case(seed=hq + d, hq=hq, hkv=hkv, d=d,
+                                         seq_lens=[40, 300, 129, 700], extend_lens=[40, 44, 1, 200],
+                                         shared_prefix=64)
+    ks, vs = scales if scales else (None, None)
+    fks, fvs = (1.0 if ks is None else ks), (1.0 if vs is None else vs)
+    layer = _layer(hq, hkv, d, ks, vs)
+    ref = OracleMHATokenToKVPool(case.pool_size, 1, FP8, hkv, d, 1)
+    ref.k_buffer[0].copy_((case.k_cache.float() / fks).to(case.dtype).to(FP8).view(torch.uint8))
+    ref.v_buffer[0].copy_((case.v_cache.float() / fvs).to(case.dtype).to(FP8).view(torch.uint8))
+    ref.set_kv_buffer(layer, case.out_cache_loc, case.k_new.clone(), case.v_new.clone(),
+                      None if ks is None else torch.tensor(ks), None if vs is None else torch.tensor(vs))
+    o_ref = OA.extend_attention_oracle(
+        case.q.view(-1, hq, d), ref.get_key_buffer(0), ref.get_value_buffer(0), case.req_to_token,
+        case.req_pool_indices, case.seq_lens, case.extend_prefix_lens, case.extend_seq_lens,
+        layer.scaling, True, 0.0, fks, fvs)
+    fp8_case = SimpleNamespace(**vars(case))
+    fp8_case.dtype = FP8
+    fp8_case.k_cache = torch.zeros_like(case.k_cache, dtype=torch.uint8)
+    fp8_case.v_cache = torch.zeros_like(case.v_cache, dtype=torch.uint8)
+    mr = harness.make_model_runner(fp8_case, "cuda")
+    pool = mr.token_to_kv_pool
+    init_k, init_v = ref.k_buffer[0].clone(), ref.v_buffer[0].clone()
+    init_k[case.out_cache_loc] = 0
+    init_v[case.out_cache_loc] = 0
+    pool.k_buffer[0].copy_(init_k)
+    pool.v_buffer[0].copy_(init_v)
+    backend = B200AttnBackend(mr)
+    t = case.q.shape[0]
+    qkv = torch.cat([case.q, case.k_new.reshape(t, -1), case.v_new.reshape(t, -1)], dim=1).cuda()
+    q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+    fb = ForwardBatch(forward_mode=ForwardMode.EXTEND, batch_size=case.bs,
+                      req_pool_indices=case.req_pool_indices.cuda(), seq_lens=case.seq_lens.cuda(),
+                      out_cache_loc=case.out_cache_loc.cuda(), seq_lens_sum=int(case.seq_lens.sum()),
+                      seq_lens_cpu=case.seq_lens, extend_seq_lens=case.extend_seq_lens.cuda(),
+                      extend_prefix_lens=case.extend_prefix_lens.cuda(),
+                      extend_seq_lens_cpu=case.extend_seq_lens.tolist(),
+                      extend_prefix_lens_cpu=case.extend_prefix_lens.tolist(),
+                      extend_num_tokens=t, req_to_token_pool=mr.req_to_token_pool,
+                      token_to_kv_pool=pool, attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    o = layer(q, k, v, fb)
+    torch.cuda.synchronize()
+    assert torch.equal(pool.k_buffer[0].cpu(), ref.k_buffer[0])
+    assert torch.equal(pool.v_buffer[0].cpu(), ref.v_buffer[0])
+    st = harness.error_stats(o.cpu(), o_ref.reshape(t, -1))
+    assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, st

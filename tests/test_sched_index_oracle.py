@@ -1,0 +1,37 @@
+"""CPU: the scheduler-index oracle against the fixtures produced by the reference's own torch
+implementations (oracle/gen_golden_sched_index.py), plus allocator invariants."""
+import os
+
+import torch
+
+from oracle import sched_index as O
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "sched_index.pt")
+
+
+def test_oracle_matches_reference_fixtures():
+    for c in torch.load(GOLD):
+        last = O.get_last_loc_oracle(c["req_to_token"], c["req_pool_indices"], c["prefix_lens"])
+        assert torch.equal(last, c["last_loc"])
+        pos, start = O.compute_position_oracle(c["prefix_lens"], c["extend_seq_lens"])
+        assert torch.equal(pos, c["positions"])
+        assert torch.equal(start, c["extend_start_loc"].to(torch.int32))
+
+
+def test_alloc_oracle_invariants():
+    page = 16
+    pre = torch.tensor([0, 5, 16, 31, 40])
+    seq = torch.tensor([3, 40, 17, 32, 100])
+    # last_loc of a prefix ending mid-page: any slot with (loc + 1) % page == pre % page
+    last = torch.tensor([-1, 16 * 50 + 4, 16 * 51 + 15, 16 * 52 + 14, 16 * 53 + 7])
+    free = torch.arange(100, 160)
+    out, used = O.alloc_extend_oracle(pre, seq, last, free, page)
+    assert out.numel() == int((seq - pre).sum()) and out.unique().numel() == out.numel()
+    assert used == sum((int(s) + page - 1) // page - (int(p) + page - 1) // page
+                       for p, s in zip(pre, seq))
+    # request 1 continues its page, then takes whole pages
+    seg = out[3:3 + 35]
+    assert seg[0] == last[1] + 1 and (seg[11] % page) == 0
+    dec, used_d = O.alloc_decode_oracle(torch.tensor([17, 18, 33]), torch.tensor([15, 16 * 9, 16 * 7 + 15]),
+                                        torch.tensor([70, 71]), page)
+    assert dec.tolist() == [70 * 16, 16 * 9 + 1, 71 * 16] and used_d == 2
