@@ -82,9 +82,17 @@ class RotaryEmbedding(nn.Module):
         pool = forward_batch.token_to_kv_pool
         k_cache = pool.get_key_buffer(layer.layer_id)
         v_cache = pool.get_value_buffer(layer.layer_id)
+        loc = forward_batch.out_cache_loc
+        if k_cache.dtype == torch.float8_e4m3fn:
+            # FP8 pool: rotate in place, then the quantising scatter (b200_kv_write_fp8) — two
+            # launches; scales as in FlashInfer's set_kv_buffer call (flashinfer_backend.py:427)
+            self._launch(positions, query, key, None, None, None, None)
+            ks = getattr(layer, "k_scale_float", None)
+            vs = getattr(layer, "v_scale_float", None)
+            pool.set_kv_buffer(layer, loc, key, value, ks, vs)
+            return query, key
         if k_cache.dtype != key.dtype:
             raise _lib.B200Error("forward_with_kv_write: KV pool dtype differs from the activations")
-        loc = forward_batch.out_cache_loc
         if loc.dtype != torch.int64:
             loc = loc.to(torch.int64)
         self._launch(positions, query, key, value, k_cache.view(k_cache.shape[0], -1),

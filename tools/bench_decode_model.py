@@ -85,6 +85,8 @@ def main():
     ap.add_argument("--no-fuse", action="store_true")
     ap.add_argument("--pdl", type=int, default=1, help="programmatic dependent launch on/off")
     ap.add_argument("--max-kv-gb", type=float, default=80.0)
+    ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"],
+                    help="KV pool dtype (fp8 = float8_e4m3fn, --kv-cache-dtype fp8_e4m3)")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
 
@@ -114,7 +116,8 @@ def main():
     bss = [int(x) for x in args.bs.split(",")]
     ctxs = [int(x) for x in args.ctx.split(",")]
     # KV pool sized for the largest (bs, ctx) point that fits the budget
-    per_tok = 2 * hkv * d * 2 * layers
+    kv_fp8 = args.kv_dtype == "fp8"
+    per_tok = 2 * hkv * d * (1 if kv_fp8 else 2) * layers
     points = [(b, c) for c in ctxs for b in bss if b * c * per_tok <= args.max_kv_gb * 1e9]
     pool_tokens = max(b * c for b, c in points)
     max_bs, max_ctx = max(b for b, _ in points), max(c for _, c in points)
@@ -123,10 +126,15 @@ def main():
     qc = quant_config(args.quant)
     rope = RotaryEmbedding(d, d, max_ctx + 8, theta, True, torch.bfloat16).to(dev)
     rtp = ReqToTokenPool(max_bs + 1, max_ctx + 8, dev)
-    kvp = MHATokenToKVPool(pool_tokens + max_bs, 1, torch.bfloat16, hkv, d, layers, dev)
+    kvp = MHATokenToKVPool(pool_tokens + max_bs, 1, FP8 if kv_fp8 else torch.bfloat16, hkv, d,
+                           layers, dev)
     for l in range(layers):
-        kvp.k_buffer[l].normal_()
-        kvp.v_buffer[l].normal_()
+        for buf in (kvp.k_buffer[l], kvp.v_buffer[l]):
+            if kv_fp8:  # random e4m3 bytes without the NaN patterns
+                buf.random_(0, 256)
+                buf[(buf & 0x7f) == 0x7f] = 0x38
+            else:
+                buf.normal_()
     cfg = SimpleNamespace(num_attention_heads=heads, context_len=max_ctx + 4,
                           get_num_kv_heads=lambda t: max(1, kv_heads // t))
     backend = B200AttnBackend(SimpleNamespace(
@@ -193,7 +201,8 @@ def main():
         split = {}
         for name in ("rmsnorm", "fp8_gemm_smallm", "fp8_block_gemm_smallm", "fp8_gemm",
                      "fp8_block_gemm", "w4a16_gemm", "w4a16_gemv", "rope_kv_write",
-                     "attn_decode_split", "attn_merge", "fp8_quant", "silu_and_mul", "kv_write"):
+                     "attn_decode_split", "attn_decode_fp8kv", "kv_write_fp8", "attn_merge", "all_reduce_ll",
+                     "all_reduce_oneshot", "fp8_quant", "silu_and_mul", "kv_write"):
             n, ms = _lib.timing_read(name)
             if n:
                 split[name] = {"launches": n, "us_total": round(ms * 1e3, 1)}
@@ -225,7 +234,7 @@ def main():
             ms = float(t.item())
         kv_bytes = bs * ctx * per_tok
         floor_ms = (lin_bytes + kv_bytes + lm_head.numel() * 2) / (peak * 1e9) * 1e3
-        row = {"model": args.model, "quant": args.quant, "tp": tp, "bs": bs, "ctx": ctx,
+        row = {"model": args.model, "quant": args.quant, "kv_dtype": args.kv_dtype, "tp": tp, "bs": bs, "ctx": ctx,
                "layers": layers, "fused": not args.no_fuse, "pdl": args.pdl, "ms_per_step": round(ms, 4),
                "tokens_per_s": round(bs / ms * 1e3, 1), "hbm_floor_ms": round(floor_ms, 4),
                "frac_of_hbm_floor": round(floor_ms / ms, 4), "num_kv_splits": num_splits,
