@@ -153,12 +153,15 @@ all_reduce_ll_kernel(const CommDev c, const uint4* __restrict__ in, uint4* __res
 
 // LL is used while its doubled wire size is cheaper than the flag protocol's fence + flag round
 // trip (env B200_COMM_LL_MAX overrides the payload threshold in bytes).
-static int64_t ll_max_bytes() {
+// Default 4 MiB / world: a rank receives (world - 1) x 2 x payload over its NVLink ports, so the
+// break-even payload shrinks with the group size (measured at TP = 2: LL 6.1 us at 512 KiB, flag
+// protocol 11.1 us at 1 MiB).
+static int64_t ll_max_bytes(int world) {
   static int64_t v = [] {
     const char* e = std::getenv("B200_COMM_LL_MAX");
-    return (e && *e) ? std::atoll(e) : static_cast<int64_t>(512 * 1024);
+    return (e && *e) ? std::atoll(e) : static_cast<int64_t>(-1);
   }();
-  return v;
+  return v >= 0 ? v : static_cast<int64_t>(4 << 20) / world;
 }
 
 }  // namespace b200
@@ -265,7 +268,7 @@ int b200_comm_all_reduce(void* comm, const void* in, void* out, int64_t numel, i
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const uint4* i4 = static_cast<const uint4*>(in);
   uint4* o4 = static_cast<uint4*>(out);
-  if (bytes <= ll_max_bytes() && static_cast<uint64_t>(2 * bytes) <= c->dev.slot_bytes) {
+  if (bytes <= ll_max_bytes(c->dev.world) && static_cast<uint64_t>(2 * bytes) <= c->dev.slot_bytes) {
     int64_t ctas64 = (num_vec + 127) / 128;
     const int64_t cap = 4 * static_cast<int64_t>(device_sm_count());
     const int ctas = static_cast<int>(ctas64 < cap ? ctas64 : cap);

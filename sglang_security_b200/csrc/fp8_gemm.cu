@@ -232,6 +232,13 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
   const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);
   const bool big = tiles256 >= device_sm_count();
   int rc;
+  // pairs of M blocks share the weight tile by TMA multicast (B200_GEMM_MCAST=0 turns it off)
+  static const int mcast_on = env_int("B200_GEMM_MCAST", 1);
+  if (big && mcast_on && ceil_div(M, 128) % 2 == 0) {
+    rc = out_dtype == B200_BF16
+             ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16, true>(a, lda, b, ldb, ep, st, "fp8_gemm")
+             : launch_gemm_tn<kKindFp8, 256, 4, __half, true>(a, lda, b, ldb, ep, st, "fp8_gemm");
+  } else
   if (out_dtype == B200_BF16) {
     rc = big ? launch_gemm_tn<kKindFp8, 256, 4, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm")
              : launch_gemm_tn<kKindFp8, 128, 6, __nv_bfloat16>(a, lda, b, ldb, ep, st, "fp8_gemm", true);

@@ -113,7 +113,12 @@ __device__ __forceinline__ uint32_t pack_out2<__half>(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int KIND, int BLOCK_N, int STAGES, typename OutT>
+// MC (large M): CTA pairs (cluster of 2 along M, same N block) share the weight tile — each CTA
+// loads HALF of the B rows and TMA-multicasts them into both CTAs, cutting the per-SM L2->SM
+// ingest from 48 KiB to 32 KiB per K block (the measured limiter of the 128x256 tile).  A stage
+// may be refilled only when BOTH CTAs' MMAs have consumed it: tcgen05.commit multicasts its arrive
+// to both empty barriers (count 2).  tmap_b then describes BLOCK_N/2-row boxes.
+template <int KIND, int BLOCK_N, int STAGES, typename OutT, bool MC = false>
 __global__ void __launch_bounds__(192, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmEpilogueParams ep) {
@@ -137,14 +142,19 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const int num_tiles = m_blocks * n_blocks;
   const int num_kb = ceil_div(ep.K, C::BLOCK_K);
   const int S = ep.splits;
-  const int num_items = num_tiles * S;
+  // MC: items are PAIR tiles (two adjacent M blocks x one N block); this CTA takes M block
+  // 2*pair + cluster rank.  Item stride is the number of clusters.
+  const int mc_rank = MC ? static_cast<int>(cluster_ctarank()) : 0;
+  const int num_items = MC ? (m_blocks / 2) * n_blocks : num_tiles * S;
+  const int item0 = MC ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int item_step = MC ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmap_a);
     tc::prefetch_tmap(&tmap_b);
     for (int s = 0; s < STAGES; ++s) {
       tc::mbar_init(full_bar(s), 1);
-      tc::mbar_init(empty_bar(s), 1);
+      tc::mbar_init(empty_bar(s), MC ? 2 : 1);
     }
     for (int a = 0; a < 2; ++a) {
       tc::mbar_init(tfull_bar(a), 1);
@@ -158,6 +168,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   }
   tc::tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();  // the peer's barriers are initialised before anything targets them
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   griddep_wait();  // activations / scales come from the previous kernel
@@ -168,9 +179,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-        const int tile = item / S, ks = item - tile * S;
-        const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+      for (int item = item0; item < num_items; item += item_step) {
+        const int tile = MC ? item : item / S, ks = MC ? 0 : item - tile * S;
+        const int m_blk = MC ? 2 * (tile % (m_blocks / 2)) + mc_rank : tile % m_blocks;
+        const int n_blk = MC ? tile / (m_blocks / 2) : tile / m_blocks;
         const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
         const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -178,6 +190,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           tc::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * C::BLOCK_K, m_blk * C::BLOCK_M);
+          if (MC)
+            tc::tma_load_2d_mcast(sa + C::A_BYTES + mc_rank * (C::B_BYTES / 2), &tmap_b,
+                                  full_bar(stage), kb * C::BLOCK_K,
+                                  n_blk * BLOCK_N + mc_rank * (BLOCK_N / 2), 0x3);
+          else
           tc::tma_load_2d(sa + C::A_BYTES, &tmap_b, full_bar(stage), kb * C::BLOCK_K,
                           n_blk * BLOCK_N);
           if (++stage == STAGES) {
@@ -195,8 +212,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
-      for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
-        const int ks = item % S;
+      for (int item = item0; item < num_items; item += item_step, ++local) {
+        const int ks = MC ? 0 : item % S;
         const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
         const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
         const int acc = local & 1;
@@ -218,6 +235,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             else
               tc::mma_f16(tmem_d, adesc, bdesc, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
           }
+          if (MC) tc::mma_commit_mcast(empty_bar(stage), 0x3);  // frees the slot in BOTH CTAs
+          else
           tc::mma_commit(empty_bar(stage));  // smem slot free once these MMAs have read it
           if (++stage == STAGES) {
             stage = 0;
@@ -233,9 +252,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     OutT* out = static_cast<OutT*>(ep.out);
     const OutT* bias = static_cast<const OutT*>(ep.bias);
     int local = 0;
-    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
-      const int tile = item / S, ks = item - tile * S;
-      const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+    for (int item = item0; item < num_items; item += item_step, ++local) {
+      const int tile = MC ? item : item / S, ks = MC ? 0 : item - tile * S;
+      const int m_blk = MC ? 2 * (tile % (m_blocks / 2)) + mc_rank : tile % m_blocks;
+      const int n_blk = MC ? tile / (m_blocks / 2) : tile / m_blocks;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1u;
       tc::mbar_wait(tfull_bar(acc), acc_phase);
@@ -367,6 +387,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     cluster_sync_all();
     cluster_sync_all();
   }
+  if (MC) {  // the peer may still multicast into / arrive on this CTA's shared memory
+    __syncwarp();
+    cluster_sync_all();
+  }
 
   tc::tc_fence_before();
   __syncthreads();
@@ -377,7 +401,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 int splitk_pick(int tiles, int num_kb, int sms);
 
 // Host launcher: builds the two TMA descriptors and launches one CTA per SM (or per tile).
-template <int KIND, int BLOCK_N, int STAGES, typename OutT>
+template <int KIND, int BLOCK_N, int STAGES, typename OutT, bool MC = false>
 int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
                    const GemmEpilogueParams& ep_in, cudaStream_t st, const char* timer_name,
                    bool allow_split = false) {
@@ -386,9 +410,9 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
   CUtensorMap ta, tb;
   int rc = make_tmap_2d(&ta, a, ep.M, ep.K, lda * C::ELT, C::BLOCK_M, C::BLOCK_K, C::ELT, false);
   if (rc) return rc;
-  rc = make_tmap_2d(&tb, b, ep.N, ep.K, ldb * C::ELT, BLOCK_N, C::BLOCK_K, C::ELT, true);
+  rc = make_tmap_2d(&tb, b, ep.N, ep.K, ldb * C::ELT, MC ? BLOCK_N / 2 : BLOCK_N, C::BLOCK_K, C::ELT, true);
   if (rc) return rc;
-  auto kern = gemm_tn_kernel<KIND, BLOCK_N, STAGES, OutT>;
+  auto kern = gemm_tn_kernel<KIND, BLOCK_N, STAGES, OutT, MC>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -434,10 +458,14 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
   }
   const int items = tiles * ep.splits;
   // split-K: one item per CTA, clusters of `splits` CTAs; else persistent over the tiles
-  const int grid = ep.splits > 1 ? items : (items < sms ? items : sms);
+  int grid = ep.splits > 1 ? items : (items < sms ? items : sms);
+  if (MC) {  // CTA pairs: an even grid, one cluster per pair of adjacent M blocks
+    const int pairs = (ceil_div(ep.M, C::BLOCK_M) / 2) * ceil_div(ep.N, BLOCK_N);
+    grid = 2 * (pairs < sms / 2 ? pairs : sms / 2);
+  }
   {
     ScopedKernelTimer timer(timer_name, st);
-    B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, ep.splits, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));
+    B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, MC ? 2 : ep.splits, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));
   }
   B200_CHECK_LAUNCH("gemm_tn_kernel");
   return 0;
