@@ -57,6 +57,30 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t col
   return 0;
 }
 
+// Same, without swizzle: the box lands as dense rows of box_cols * elt_bytes bytes (a multiple of 16).
+int make_tmap_2d_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                       uint64_t pitch_bytes, uint32_t box_rows, uint32_t box_cols, int elt_bytes) {
+  EncodeTiledFn enc = get_encode_tiled();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15u) == 0 && pitch_bytes % 16 == 0,
+               "TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch "
+               "(pitch=%llu)", static_cast<unsigned long long>(pitch_bytes));
+  B200_REQUIRE((box_cols * elt_bytes) % 16 == 0 && box_rows <= 256 && box_cols <= 256,
+               "bad TMA box %ux%u", box_rows, box_cols);
+  const CUtensorMapDataType dt = elt_bytes == 1   ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                 : elt_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16
+                                                  : CU_TENSOR_MAP_DATA_TYPE_UINT32;
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
 // ---- small-M dispatch knobs (env overrides are for sweeps/tests; defaults are the tuned values) --
 static int env_int(const char* name, int dflt) {
   const char* v = std::getenv(name);

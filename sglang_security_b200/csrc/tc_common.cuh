@@ -234,5 +234,7 @@ __device__ __forceinline__ bool elect_one() {
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                  uint64_t pitch_bytes, uint32_t box_rows, uint32_t box_cols, int elt_bytes,
                  bool is_weight);
+int make_tmap_2d_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                       uint64_t pitch_bytes, uint32_t box_rows, uint32_t box_cols, int elt_bytes);
 
 }  // namespace b200

@@ -22,6 +22,7 @@
 //                             dequantised in registers by 4 warps straight into 128-byte-swizzled
 //                             shared memory as an MN-major B operand; TMEM accumulators; same
 //                             mbarrier rings as gemm_tc.cuh.
+#include <cstdlib>
 #include <type_traits>
 
 #include "gemm_tc.cuh"
@@ -77,11 +78,15 @@ __device__ __forceinline__ uint32_t hmul2_u32<__nv_bfloat16>(uint32_t a, uint32_
 // output-column order.  zb = biased zeros (MAGIC + z), s = scales, both 4 packed pairs.
 template <typename T>
 __device__ __forceinline__ uint4 dequant8(uint32_t q, const uint4& zb, const uint4& s) {
-  constexpr uint32_t kMagic = W4Magic<T>::kBits;
-  const uint32_t w0 = (q & 0x000f000fu) | kMagic;
-  const uint32_t w1 = ((q >> 4) & 0x000f000fu) | kMagic;
-  const uint32_t w2 = ((q >> 8) & 0x000f000fu) | kMagic;
-  const uint32_t w3 = ((q >> 12) & 0x000f000fu) | kMagic;
+  // (x & 0x000f000f) | MAGIC as ONE LOP3 (mask and magic live in registers, LUT 0xEA = (a & b) | c)
+  uint32_t mask = 0x000f000fu, magic = W4Magic<T>::kBits;
+  asm("" : "+r"(mask), "+r"(magic));  // keep them out of the immediate field
+  auto nib = [&](uint32_t x) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;\n" : "=r"(d) : "r"(x), "r"(mask), "r"(magic));
+    return d;
+  };
+  const uint32_t w0 = nib(q), w1 = nib(q >> 4), w2 = nib(q >> 8), w3 = nib(q >> 12);
   uint4 r;
   r.x = hmul2_u32<T>(hsub2_u32<T>(w0, zb.x), s.x);
   r.y = hmul2_u32<T>(hsub2_u32<T>(w1, zb.y), s.y);
@@ -149,6 +154,14 @@ __global__ void gptq_repack_kernel(const uint32_t* __restrict__ qweight,
 }
 
 // ---- fused tcgen05 W4A16 GEMM -------------------------------------------------------------------
+// Warp roles (480 threads): 0 = TMA producer of activation tiles, 1 = MMA issuer, 2..5 = epilogue,
+// 6..13 = dequant (int4 -> 16-bit -> swizzled MN-major operand), 14 = producer of the PACKED weight
+// ring.  Three independent rings: x tiles (TMA, deep enough to cover the TMA latency), dequantised
+// weight stages, and the packed ring, which is much deeper than both (4 KiB per K block), so
+// ~50 KiB of weight bytes per SM are in flight ahead of the dequant warps: the kernel streams the
+// packed weights at HBM speed when M is small and hides the dequant under the MMAs when M is large.
+// BM = 256 (two 128-row accumulators sharing one dequantised B stage) halves the dequant work per
+// flop for large M.
 struct W4GemmParams {
   const uint32_t* qweight;  // [K, N/8] B200 order
   const void* zeros;        // [G, N] biased
@@ -157,24 +170,52 @@ struct W4GemmParams {
   void* out;
   int64_t ldc;
   int M, N, K, group;
+  int raw_tma;              // 1: packed tiles by TMA (N % 32 == 0), 0: by the producer warp's lanes
+  int debug;
 };
 
-constexpr int kW4Stages = 5;
-constexpr int kW4Threads = 320;  // TMA, MMA, 4 epilogue, 4 dequant warps
+constexpr int kW4PackedBytes = 64 * 64;           // 64 k rows x 16 int32 (= 128 output columns)
+constexpr int kW4RawBytes = kW4PackedBytes + 512;  // + the K block's (zero, scale) rows, 256 B each
 
-template <typename T>
-__global__ void __launch_bounds__(kW4Threads, 1)
-w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams p) {
-  constexpr int BM = 128, BN = 128, BK = 64, STAGES = kW4Stages;
-  constexpr int A_BYTES = BM * 128, B_BYTES = BK * BN * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+// BM = rows of x per tile (128 or 256); in SWAP mode BM = MT (32 or 64) tokens and the roles of the
+// operands are exchanged: the dequantised weights are the 128-row MN-major A operand, x is the
+// K-major B operand with UMMA N = MT, so the MMA time scales with the token count.
+template <int BM, bool SWAP>
+struct W4Cfg {
+  static constexpr int BN = 128, BK = 64;
+  static constexpr int X_BYTES = BM * 128, B_BYTES = BK * BN * 2;
+  static constexpr int XS = SWAP ? (BM == 32 ? 8 : 6) : (BM == 256 ? 3 : 4);   // x stages
+  static constexpr int BS = SWAP ? 8 : (BM == 256 ? 6 : 7);                    // dequantised stages
+  static constexpr int RAWS = (!SWAP && BM == 256) ? 6 : 8;                    // packed-weight stages
+  static constexpr int ACC_COLS = BM;  // fp32 columns per accumulator set
+  static constexpr int TMEM_COLS = 2 * ACC_COLS < 32 ? 32 : 2 * ACC_COLS;
+  static constexpr int NBARS = 2 * XS + 2 * BS + 2 * RAWS + 4;
+  static constexpr int SMEM = XS * X_BYTES + BS * B_BYTES + RAWS * kW4RawBytes + NBARS * 8 + 16 + 1024;
+};
+
+template <typename T, int BM, bool SWAP, int DQ, int DG>
+__global__ void __launch_bounds__((7 + DQ) * 32, 1)
+w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_q,
+                  const __grid_constant__ CUtensorMap tmap_z, const __grid_constant__ CUtensorMap tmap_s,
+                  const W4GemmParams p) {
+  using C = W4Cfg<BM, SWAP>;
+  constexpr int BN = C::BN, BK = C::BK, XS = C::XS, BS = C::BS, RAWS = C::RAWS;
+  constexpr int MH = SWAP ? 1 : BM / 128;          // 128-row x boxes (and accumulators) per stage
+  constexpr int XBOX = SWAP ? BM : 128;            // rows of one x TMA box
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;
-  auto full_bar = [&](int s) { return bars + 8u * s; };
-  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
-  auto tfull_bar = [&](int a) { return bars + 8u * (2 * STAGES + a); };
-  auto tempty_bar = [&](int a) { return bars + 8u * (2 * STAGES + 2 + a); };
-  const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+  const uint32_t b_base = smem_base + XS * C::X_BYTES;
+  const uint32_t raw_base = b_base + BS * C::B_BYTES;
+  const uint32_t bars = raw_base + RAWS * kW4RawBytes;
+  auto xfull_bar = [&](int s) { return bars + 8u * s; };
+  auto xempty_bar = [&](int s) { return bars + 8u * (XS + s); };
+  auto bfull_bar = [&](int s) { return bars + 8u * (2 * XS + s); };
+  auto bempty_bar = [&](int s) { return bars + 8u * (2 * XS + BS + s); };
+  auto rfull_bar = [&](int s) { return bars + 8u * (2 * XS + 2 * BS + s); };
+  auto rempty_bar = [&](int s) { return bars + 8u * (2 * XS + 2 * BS + RAWS + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * XS + 2 * BS + 2 * RAWS + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * XS + 2 * BS + 2 * RAWS + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * C::NBARS;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -183,12 +224,22 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
   const int m_blocks = ceil_div(p.M, BM), n_blocks = ceil_div(p.N, BN);
   const int num_tiles = m_blocks * n_blocks;
   const int num_kb = ceil_div(p.K, BK);
+  const int NC = p.N / 8;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmap_x);
-    for (int s = 0; s < STAGES; ++s) {
-      tc::mbar_init(full_bar(s), 1 + 128);  // TMA expect_tx arrive + 128 dequant threads
-      tc::mbar_init(empty_bar(s), 1);
+    if (p.raw_tma) tc::prefetch_tmap(&tmap_q);
+    for (int s = 0; s < XS; ++s) {
+      tc::mbar_init(xfull_bar(s), 1);
+      tc::mbar_init(xempty_bar(s), 1);
+    }
+    for (int s = 0; s < BS; ++s) {
+      tc::mbar_init(bfull_bar(s), DQ / DG);  // one arrive per dequant warp of the owning group
+      tc::mbar_init(bempty_bar(s), 1);
+    }
+    for (int s = 0; s < RAWS; ++s) {
+      tc::mbar_init(rfull_bar(s), 1);
+      tc::mbar_init(rempty_bar(s), DQ / DG);
     }
     for (int a = 0; a < 2; ++a) {
       tc::mbar_init(tfull_bar(a), 1);
@@ -197,7 +248,7 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
     tc::fence_barrier_init();
   }
   if (warp == 1) {
-    tc::tmem_alloc(tmem_slot, 2 * BN);
+    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
     tc::tmem_relinquish();
   }
   tc::tc_fence_before();
@@ -213,14 +264,84 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m_blk = tile % m_blocks;
         for (int kb = 0; kb < num_kb; ++kb) {
-          tc::mbar_wait(empty_bar(stage), phase ^ 1u);
-          tc::mbar_arrive_expect_tx(full_bar(stage), A_BYTES);
-          tc::tma_load_2d(smem_base + stage * STAGE_BYTES, &tmap_x, full_bar(stage), kb * BK,
-                          m_blk * BM);
-          if (++stage == STAGES) {
+          tc::mbar_wait(xempty_bar(stage), phase ^ 1u);
+          if (p.debug & 8) { tc::mbar_arrive(xfull_bar(stage)); } else {
+          tc::mbar_arrive_expect_tx(xfull_bar(stage), C::X_BYTES);
+#pragma unroll
+          for (int h = 0; h < MH; ++h)
+            tc::tma_load_2d(smem_base + stage * C::X_BYTES + h * (128 * 128), &tmap_x,
+                            xfull_bar(stage), kb * BK, m_blk * BM + h * XBOX);
+          }
+          if (++stage == XS) {
             stage = 0;
             phase ^= 1u;
           }
+        }
+      }
+    }
+  } else if (warp == 6 + DQ) {
+    // ===================== producer of the packed-weight ring =====================
+    // Every stage also carries the K block's (zero, scale) rows (group sizes that are a multiple of
+    // the K block): the dequant warps then touch shared memory only, so the MEMBAR that
+    // fence.proxy.async implies never waits on a global load.
+    const bool zs_rows = (p.group % BK) == 0;
+    const int kb_per_group = zs_rows ? p.group / BK : 1;
+    int rs = 0;
+    uint32_t rphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int n_blk = tile / m_blocks;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const uint32_t dst = raw_base + rs * kW4RawBytes;
+        const int g = kb / kb_per_group;
+        if (p.raw_tma) {
+          if (lane == 0) {
+            tc::mbar_wait(rempty_bar(rs), rphase ^ 1u);
+            if (p.debug & 4) { tc::mbar_arrive(rfull_bar(rs)); } else {
+            tc::mbar_arrive_expect_tx(rfull_bar(rs), zs_rows ? kW4RawBytes : kW4PackedBytes);
+            if (p.raw_tma == 2) {  // EXPERIMENT: tile-major packed weights, one 4 KiB bulk copy
+              const char* src = reinterpret_cast<const char*>(p.qweight) +
+                                (static_cast<int64_t>(n_blk) * num_kb + kb) * kW4PackedBytes;
+              asm volatile(
+                  "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+                  "l"(src), "r"(kW4PackedBytes), "r"(rfull_bar(rs))
+                  : "memory");
+            } else
+            tc::tma_load_2d_hint(dst, &tmap_q, rfull_bar(rs), n_blk * (BN / 8), kb * BK,
+                                 m_blocks > 1 ? tc::kEvictLast : tc::kEvictFirst);
+            if (zs_rows) {
+              tc::tma_load_2d(dst + kW4PackedBytes, &tmap_z, rfull_bar(rs), n_blk * BN, g);
+              tc::tma_load_2d(dst + kW4PackedBytes + 256, &tmap_s, rfull_bar(rs), n_blk * BN, g);
+            }
+            }
+          }
+        } else {
+          // rows whose pitch is not a multiple of 16 bytes: the 32 lanes copy the tile word by word
+          tc::mbar_wait(rempty_bar(rs), rphase ^ 1u);
+          uint32_t v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int w = i * 32 + lane, r = w >> 4, cc = n_blk * (BN / 8) + (w & 15);
+            const int k = kb * BK + r;
+            v[i] = (k < p.K && cc < NC) ? __ldg(p.qweight + static_cast<int64_t>(k) * NC + cc) : 0u;
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst + (i * 32 + lane) * 4), "r"(v[i])
+                         : "memory");
+          if (zs_rows) {  // lanes 0..15: zeros, 16..31: scales, 8 columns (16 bytes) each
+            const int cc = n_blk * (BN / 8) + (lane & 15);
+            const uint4* src = static_cast<const uint4*>(lane < 16 ? p.zeros : p.scales);
+            const uint4 zs = cc < NC ? __ldg(src + static_cast<int64_t>(g) * NC + cc) : make_uint4(0, 0, 0, 0);
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + kW4PackedBytes + lane * 16),
+                         "r"(zs.x), "r"(zs.y), "r"(zs.z), "r"(zs.w)
+                         : "memory");
+          }
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(rfull_bar(rs));
+        }
+        if (++rs == RAWS) {
+          rs = 0;
+          rphase ^= 1u;
         }
       }
     }
@@ -228,31 +349,48 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
     // ===================== MMA issuer =====================
     if (lane == 0) {
       constexpr uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
-      constexpr uint32_t idesc = tc::make_idesc(fmt, fmt, BM, BN, 0, 1);  // B is MN-major
-      int stage = 0;
-      uint32_t phase = 0;
+      // normal: A = x (K-major, 128 rows), B = weights (MN-major, N = 128)
+      // swap  : A = weights (MN-major, M = 128 output columns), B = x (K-major, N = MT tokens)
+      constexpr uint32_t idesc = SWAP ? tc::make_idesc(fmt, fmt, 128, BM, 1, 0)
+                                      : tc::make_idesc(fmt, fmt, 128, BN, 0, 1);
+      int xs = 0, bs = 0;
+      uint32_t xphase = 0, bphase = 0;
       int local = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
         const int acc = local & 1;
         tc::mbar_wait(tempty_bar(acc), ((local >> 1) & 1u) ^ 1u);
         tc::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * BN;
+        const uint32_t tmem_d = tmem_base + acc * C::ACC_COLS;
         for (int kb = 0; kb < num_kb; ++kb) {
-          tc::mbar_wait(full_bar(stage), phase);
+          tc::mbar_wait(xfull_bar(xs), xphase);
+          tc::mbar_wait(bfull_bar(bs), bphase);
           tc::tc_fence_after();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          const uint32_t sb = sa + A_BYTES;
+          const uint32_t sx = smem_base + xs * C::X_BYTES;
+          const uint32_t sw = b_base + bs * C::B_BYTES;
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
-            const uint64_t adesc = tc::make_smem_desc_sw128(sa + kk * 32, 1024, 16);
-            // B rows kk*16.. of the [64 k x 128 n] tile; panels of 64 n are 64*128 bytes apart
-            const uint64_t bdesc = tc::make_smem_desc_sw128(sb + kk * 16 * 128, 1024, BK * 128);
-            tc::mma_f16(tmem_d, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            // weight rows kk*16.. of the [64 k x 128 n] tile; panels of 64 n are 64*128 bytes apart
+            const uint64_t wdesc = tc::make_smem_desc_sw128(sw + kk * 16 * 128, 1024, BK * 128);
+#pragma unroll
+            for (int h = 0; h < MH; ++h) {
+              const uint64_t xdesc =
+                  tc::make_smem_desc_sw128(sx + h * (128 * 128) + kk * 32, 1024, 16);
+              if (p.debug & 2) continue;
+              if (SWAP)
+                tc::mma_f16(tmem_d, wdesc, xdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+              else
+                tc::mma_f16(tmem_d + h * BN, xdesc, wdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            }
           }
-          tc::mma_commit(empty_bar(stage));
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1u;
+          tc::mma_commit(xempty_bar(xs));
+          tc::mma_commit(bempty_bar(bs));
+          if (++xs == XS) {
+            xs = 0;
+            xphase ^= 1u;
+          }
+          if (++bs == BS) {
+            bs = 0;
+            bphase ^= 1u;
           }
         }
         tc::mma_commit(tfull_bar(acc));
@@ -269,40 +407,66 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
       const int acc = local & 1;
       tc::mbar_wait(tfull_bar(acc), (local >> 1) & 1u);
       tc::tc_fence_after();
-      const int row = m_blk * BM + quarter * 32 + lane;
-      const bool row_ok = row < p.M;
-      T* orow = out + static_cast<int64_t>(row) * p.ldc;
+      if (SWAP) {
+        // accumulator lanes = output columns, TMEM columns = tokens
+        const int n = n_blk * BN + quarter * 32 + lane;
+        const float bv = (bias && n < p.N) ? to_float<T>(bias[n]) : 0.f;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tc::tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN + c * 32,
-                      r);
-        tc::tmem_ld_wait();
-        const int col0 = n_blk * BN + c * 32;
-        if (row_ok && col0 < p.N) {
-          if (col0 + 32 <= p.N && (p.ldc & 7) == 0) {
-#pragma unroll
-            for (int v = 0; v < 4; ++v) {
-              uint32_t packed[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const int j = v * 8 + e * 2;
-                float x0 = __uint_as_float(r[j]), x1 = __uint_as_float(r[j + 1]);
-                if (bias) {
-                  x0 += to_float<T>(bias[col0 + j]);
-                  x1 += to_float<T>(bias[col0 + j + 1]);
-                }
-                packed[e] = pack_out2<T>(x0, x1);
-              }
-              *reinterpret_cast<uint4*>(orow + col0 + v * 8) =
-                  make_uint4(packed[0], packed[1], packed[2], packed[3]);
-            }
-          } else {
+        for (int c = 0; c < BM / 32; ++c) {
+          if (c * 32 >= p.M) break;
+          uint32_t r[32];
+          tc::tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                            acc * C::ACC_COLS + c * 32,
+                        r);
+          tc::tmem_ld_wait();
+          if (n < p.N) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (col0 + j >= p.N) break;
-              const float b = bias ? to_float<T>(bias[col0 + j]) : 0.f;
-              orow[col0 + j] = from_float<T>(__uint_as_float(r[j]) + b);
+              const int m = c * 32 + j;
+              if (m < p.M) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(__uint_as_float(r[j]) + bv);
+            }
+          }
+        }
+      } else
+#pragma unroll 1
+      for (int h = 0; h < MH; ++h) {
+        const int row = m_blk * BM + h * 128 + quarter * 32 + lane;
+        const bool row_ok = row < p.M;
+        T* orow = out + static_cast<int64_t>(row) * p.ldc;
+        if (m_blk * BM + h * 128 >= p.M) break;  // whole half is padding (warp-uniform)
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tc::tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
+                            acc * C::ACC_COLS + h * BN + c * 32,
+                        r);
+          tc::tmem_ld_wait();
+          const int col0 = n_blk * BN + c * 32;
+          if (row_ok && col0 < p.N) {
+            if (col0 + 32 <= p.N && (p.ldc & 7) == 0) {
+#pragma unroll
+              for (int v = 0; v < 4; ++v) {
+                uint32_t packed[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const int j = v * 8 + e * 2;
+                  float x0 = __uint_as_float(r[j]), x1 = __uint_as_float(r[j + 1]);
+                  if (bias) {
+                    x0 += to_float<T>(bias[col0 + j]);
+                    x1 += to_float<T>(bias[col0 + j + 1]);
+                  }
+                  packed[e] = pack_out2<T>(x0, x1);
+                }
+                *reinterpret_cast<uint4*>(orow + col0 + v * 8) =
+                    make_uint4(packed[0], packed[1], packed[2], packed[3]);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (col0 + j >= p.N) break;
+                const float b = bias ? to_float<T>(bias[col0 + j]) : 0.f;
+                orow[col0 + j] = from_float<T>(__uint_as_float(r[j]) + b);
+              }
             }
           }
         }
@@ -312,89 +476,167 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const W4GemmParams
       if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
     }
   } else {
-    // ===================== dequant warps (6..9): int4 -> 16-bit -> swizzled smem B tile ============
-    const int t = threadIdx.x - 6 * 32;  // 0..127
-    const int col = t & 15;              // int32 column inside the 128-wide n tile
-    const int row0 = t >> 4;             // 0..7, rows row0 + 8i
-    const int NC = p.N / 8;
-    const T* scales = static_cast<const T*>(p.scales);
-    const T* zeros = static_cast<const T*>(p.zeros);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int n_blk = tile / m_blocks;
-      const int c = n_blk * (BN / 8) + col;  // global int32 column
-      const bool c_ok = c < NC;
-      int g_cached = -1;
-      uint4 zb = make_uint4(0, 0, 0, 0), sc = make_uint4(0, 0, 0, 0);
-      uint32_t q[8];
-      auto load_q = [&](int kb) {
+    // ===================== dequant warps (6..6+DQ-1): packed ring -> 16-bit swizzled B stage ======
+    // The warps form DG groups; group j owns every DG-th K block of this CTA's K-block sequence
+    // (the sequence runs on across tiles), so the fixed per-block latency chain of one warp (barrier
+    // polls, ld.shared, fence.proxy.async) overlaps with the other groups' blocks.
+    constexpr int NT = (DQ / DG) * 32;    // threads per group
+    constexpr int RSTEP = NT / 16;        // row stride of one thread's rows inside a K block
+    constexpr int RPT = BK / RSTEP;       // rows per thread per K block
+    static_assert(DQ % DG == 0 && RSTEP % 8 == 0, "the swizzle term must not depend on the row index i");
+    static_assert(DG <= BS && DG <= RAWS, "a group advances its ring position by DG with one wrap");
+    const int grp = (warp - 6) / (DQ / DG);
+    const int t = threadIdx.x - 6 * 32 - grp * NT;
+    const int col = t & 15;               // int32 column inside the 128-wide n tile
+    const int row0 = t >> 4;              // rows row0 + RSTEP * i
+    const uint4* zeros = static_cast<const uint4*>(p.zeros);    // rows of NC uint4 (8 columns each)
+    const uint4* scales = static_cast<const uint4*>(p.scales);
+    const bool group_fast = (p.group % BK) == 0;  // one (zero, scale) row per K block
+    // byte offset of this thread's 16-byte chunk of row row0 inside a B stage; rows row0 + RSTEP*i
+    // keep the same swizzle term because RSTEP is a multiple of 8
+    const uint32_t b_off = (col >> 3) * (BK * 128) + row0 * 128 + (((col & 7) ^ (row0 & 7)) << 4);
+    const uint32_t r_off = row0 * 64 + col * 4;
+    int stage = grp, rs = grp;            // ring positions of this group's next K block
+    uint32_t phase = 0, rphase = 0;
+    int tile = blockIdx.x, kb = grp;
+    bool new_tile = true;
+    int cc = 0;
+    while (true) {
+      while (kb >= num_kb) {
+        kb -= num_kb;
+        tile += gridDim.x;
+        new_tile = true;
+      }
+      if (tile >= num_tiles) break;
+      if (new_tile) {
+        const int c = (tile / m_blocks) * (BN / 8) + col;  // global int32 column
+        cc = c < NC ? c : NC - 1;  // clamped: columns >= N are computed but never stored
+        new_tile = false;
+      }
+      tc::mbar_wait(rfull_bar(rs), rphase);
+      const uint32_t rsrc = raw_base + rs * kW4RawBytes + r_off;
+      uint32_t q[RPT];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int k = kb * BK + row0 + 8 * i;
-          q[i] = (c_ok && k < p.K) ? __ldg(p.qweight + static_cast<int64_t>(k) * NC + c) : 0u;
-        }
-      };
-      load_q(0);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        uint32_t qc[8];
+      for (int i = 0; i < RPT; ++i)
+        asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(q[i]) : "r"(rsrc + RSTEP * i * 64));
+      uint4 zb = make_uint4(0, 0, 0, 0), sc = zb;
+      if (group_fast) {  // this K block's (zero, scale) rows travel with the packed tile
+        const uint32_t zsrc = raw_base + rs * kW4RawBytes + kW4PackedBytes + col * 16;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                     : "=r"(zb.x), "=r"(zb.y), "=r"(zb.z), "=r"(zb.w) : "r"(zsrc));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                     : "=r"(sc.x), "=r"(sc.y), "=r"(sc.z), "=r"(sc.w) : "r"(zsrc + 256));
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(rempty_bar(rs));
+      rs += DG;
+      if (rs >= RAWS) {
+        rs -= RAWS;
+        rphase ^= 1u;
+      }
+      const uint32_t dst = b_base + stage * C::B_BYTES + b_off;
+      if (group_fast) {
+        uint4 w[RPT];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) qc[i] = q[i];
-        if (kb + 1 < num_kb) load_q(kb + 1);  // prefetch the next K block's packed weights
-        tc::mbar_wait(empty_bar(stage), phase ^ 1u);
-        const uint32_t sb = smem_base + stage * STAGE_BYTES + A_BYTES;
+        for (int i = 0; i < RPT; ++i) w[i] = dequant8<T>(q[i], zb, sc);
+        tc::mbar_wait(bempty_bar(stage), phase ^ 1u);
+        if (!(p.debug & 1))
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = row0 + 8 * i;
-          const int k = kb * BK + r;
+        for (int i = 0; i < RPT; ++i)
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + RSTEP * i * 128),
+                       "r"(w[i].x), "r"(w[i].y), "r"(w[i].z), "r"(w[i].w)
+                       : "memory");
+      } else {
+        // groups smaller than / not aligned to a K block: look the group up per row
+        int g_cached = -1;
+        tc::mbar_wait(bempty_bar(stage), phase ^ 1u);
+#pragma unroll
+        for (int i = 0; i < RPT; ++i) {
+          const int k = kb * BK + row0 + RSTEP * i;
           uint4 w = make_uint4(0, 0, 0, 0);
-          if (c_ok && k < p.K) {
+          if (k < p.K) {  // rows past K must be exact zeros (x is zero-filled there, 0 * garbage != 0)
             const int g = k / p.group;
             if (g != g_cached) {
               g_cached = g;
-              zb = *reinterpret_cast<const uint4*>(zeros + (static_cast<int64_t>(g) * NC + c) * 8);
-              sc = *reinterpret_cast<const uint4*>(scales + (static_cast<int64_t>(g) * NC + c) * 8);
+              zb = __ldg(zeros + static_cast<int64_t>(g) * NC + cc);
+              sc = __ldg(scales + static_cast<int64_t>(g) * NC + cc);
             }
-            w = dequant8<T>(qc[i], zb, sc);
+            w = dequant8<T>(q[i], zb, sc);
           }
-          const uint32_t addr =
-              sb + (col >> 3) * (BK * 128) + r * 128 + (((col & 7) ^ (r & 7)) << 4);
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(w.x), "r"(w.y),
-                       "r"(w.z), "r"(w.w)
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + RSTEP * i * 128),
+                       "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w)
                        : "memory");
         }
-        tc::fence_proxy_async_smem();
-        tc::mbar_arrive(full_bar(stage));
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1u;
-        }
       }
+      if (!(p.debug & 16)) tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(bfull_bar(stage));
+      stage += DG;
+      if (stage >= BS) {
+        stage -= BS;
+        phase ^= 1u;
+      }
+      kb += DG;
     }
   }
 
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 2 * BN);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
 }
 
-template <typename T>
-static int launch_w4a16_gemm(const void* x, int64_t ldx, const W4GemmParams& p, cudaStream_t st) {
-  constexpr int SMEM = kW4Stages * (128 * 128 + 64 * 128 * 2) + (2 * kW4Stages + 4) * 8 + 16 + 1024;
-  CUtensorMap tx;
-  int rc = make_tmap_2d(&tx, x, p.M, p.K, ldx * 2, 128, 64, 2, false);
+// Tile selection.  M <= 64: swap-AB (tokens are the UMMA N dimension).  Otherwise 128-row tiles, or
+// 256-row tiles (half the dequant work per flop) once they still fill the machine.
+// B200_W4_BM=32|64 (swap) |128|256 overrides (sweeps).
+static int w4_pick_bm(int M, int N, int sms) {
+  static int forced = [] {
+    const char* v = std::getenv("B200_W4_BM");
+    return v && *v ? std::atoi(v) : 0;
+  }();
+  if ((forced == 32 || forced == 64) && M <= forced) return forced;
+  if (forced == 128 || forced == 256) return forced;
+  if (M <= 32) return 32;
+  if (M <= 64) return 64;
+  if (M <= 128) return 128;
+  return ceil_div(M, 256) * ceil_div(N, 128) >= (sms * 3) / 4 ? 256 : 128;
+}
+
+template <typename T, int BM, bool SWAP, int DQ, int DG>
+static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStream_t st) {
+  using C = W4Cfg<BM, SWAP>;
+  CUtensorMap tx, tq;
+  int rc = make_tmap_2d(&tx, x, p.M, p.K, ldx * 2, SWAP ? BM : 128, 64, 2, false);
   if (rc) return rc;
-  auto kern = w4a16_gemm_kernel<T>;
+  p.raw_tma = (p.N % 32 == 0 && aligned16(p.qweight)) ? 1 : 0;
+  {
+    static const int tiled = [] { const char* v = std::getenv("B200_W4_TILED"); return v && *v ? std::atoi(v) : 0; }();
+    if (tiled && p.raw_tma && p.N % 128 == 0 && p.K % 64 == 0) p.raw_tma = 2;
+  }
+  if (p.raw_tma) {
+    rc = make_tmap_2d_plain(&tq, p.qweight, p.K, p.N / 8, static_cast<uint64_t>(p.N / 8) * 4, 64, 16, 4);
+    if (rc) return rc;
+  } else {
+    tq = tx;
+  }
+  CUtensorMap tz = tx, ts = tx;
+  if (p.raw_tma && p.group % 64 == 0) {
+    const uint64_t G = static_cast<uint64_t>(p.K / p.group);
+    rc = make_tmap_2d_plain(&tz, p.zeros, G, p.N, static_cast<uint64_t>(p.N) * 2, 1, 128, 2);
+    if (rc) return rc;
+    rc = make_tmap_2d_plain(&ts, p.scales, G, p.N, static_cast<uint64_t>(p.N) * 2, 1, 128, 2);
+    if (rc) return rc;
+  }
+  auto kern = w4a16_gemm_kernel<T, BM, SWAP, DQ, DG>;
   static bool attr_done = false;
   if (!attr_done) {
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
     attr_done = true;
   }
-  const int tiles = ceil_div(p.M, 128) * ceil_div(p.N, 128);
+  const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, 128);
   const int sms = device_sm_count();
   {
     ScopedKernelTimer timer("w4a16_gemm", st);
-    kern<<<tiles < sms ? tiles : sms, kW4Threads, SMEM, st>>>(tx, p);
+    kern<<<tiles < sms ? tiles : sms, (7 + DQ) * 32, C::SMEM, st>>>(tx, tq, tz, ts, p);
   }
   B200_CHECK_LAUNCH("w4a16_gemm_kernel");
   return 0;
@@ -489,8 +731,29 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
   p.K = K;
   p.group = group_size;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return dtype == B200_F16 ? launch_w4a16_gemm<__half>(x, ldx, p, st)
-                           : launch_w4a16_gemm<__nv_bfloat16>(x, ldx, p, st);
+  p.raw_tma = 0;
+  {
+    static const int dbg = [] { const char* v = std::getenv("B200_W4_DEBUG"); return v && *v ? std::atoi(v) : 0; }();
+    p.debug = dbg;
+  }
+  const int bm = w4_pick_bm(M, N, device_sm_count());
+  // dequant warp layout: DQ warps in DG groups that own alternate K blocks.  B200_W4_CFG: 0 = 8 warps /
+  // 1 group, 1 = 8 / 2 (default), 2 = 16 / 4 (16 / 2 for the 256-row tile, whose ring has 3 stages)
+  static const int cfg = [] {
+    const char* v = std::getenv("B200_W4_CFG");
+    return v && *v ? std::atoi(v) : 1;
+  }();
+#define B200_W4_LAUNCH_C(TT, DQ_, DG_, DG256_)                                          \
+  (bm == 256  ? launch_w4a16_gemm<TT, 256, false, DQ_, DG256_>(x, ldx, p, st)           \
+   : bm == 128 ? launch_w4a16_gemm<TT, 128, false, DQ_, DG_>(x, ldx, p, st)             \
+   : bm == 64  ? launch_w4a16_gemm<TT, 64, true, DQ_, DG_>(x, ldx, p, st)               \
+               : launch_w4a16_gemm<TT, 32, true, DQ_, DG_>(x, ldx, p, st))
+#define B200_W4_LAUNCH(TT)                                                              \
+  (cfg == 0 ? B200_W4_LAUNCH_C(TT, 8, 1, 1)                                             \
+   : cfg == 2 ? B200_W4_LAUNCH_C(TT, 16, 4, 2) : B200_W4_LAUNCH_C(TT, 8, 2, 2))
+  return dtype == B200_F16 ? B200_W4_LAUNCH(__half) : B200_W4_LAUNCH(__nv_bfloat16);
+#undef B200_W4_LAUNCH_C
+#undef B200_W4_LAUNCH
 }
 
 }  // extern "C"
