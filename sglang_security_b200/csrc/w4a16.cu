@@ -29,7 +29,7 @@
 
 namespace b200 {
 
-int w4a16_gemv_max_m();                                        // w4a16_gemv.cu
+int w4a16_gemv_max_m(int N);                                   // w4a16_gemv.cu
 bool w4a16_gemv_supported(int M, int N, int K, int group);
 
 template <typename T>
@@ -154,14 +154,18 @@ __global__ void gptq_repack_kernel(const uint32_t* __restrict__ qweight,
 }
 
 // ---- fused tcgen05 W4A16 GEMM -------------------------------------------------------------------
-// Warp roles (480 threads): 0 = TMA producer of activation tiles, 1 = MMA issuer, 2..5 = epilogue,
-// 6..13 = dequant (int4 -> 16-bit -> swizzled MN-major operand), 14 = producer of the PACKED weight
-// ring.  Three independent rings: x tiles (TMA, deep enough to cover the TMA latency), dequantised
-// weight stages, and the packed ring, which is much deeper than both (4 KiB per K block), so
-// ~50 KiB of weight bytes per SM are in flight ahead of the dequant warps: the kernel streams the
-// packed weights at HBM speed when M is small and hides the dequant under the MMAs when M is large.
-// BM = 256 (two 128-row accumulators sharing one dequantised B stage) halves the dequant work per
-// flop for large M.
+// Warp roles: 0 = TMA producer of activation tiles, 1 = MMA issuer, 2..5 = epilogue, 6..6+DQ-1 =
+// dequant (int4 -> 16-bit -> swizzled MN-major operand), last warp = producer of the PACKED ring.
+//   operand ring : stage = x tile (TMA) + dequantised weight tile (written by the dequant warps);
+//                  `full` counts the TMA transaction plus one arrive per dequant warp of the owning
+//                  group, `empty` is one tcgen05.commit.
+//   packed ring  : the raw int4 words of a stage plus that stage's (zero, scale) rows, all by TMA and
+//                  deeper than the operand ring, so the dequant warps only ever read shared memory
+//                  (a global load in flight would stall the MEMBAR that fence.proxy.async implies).
+// A stage spans KS sub-blocks of 64 K rows: every barrier hand-off (a fixed ~0.3 us round trip per
+// role, measured) is amortised over KS * 64 rows.  The dequant warps form DG groups that own alternate
+// stages.  BM = 256 (two 128-row accumulators sharing one dequantised stage) halves the dequant work
+// per flop for large M; SWAP exchanges the operand roles for M <= 64 (see W4Cfg).
 struct W4GemmParams {
   const uint32_t* qweight;  // [K, N/8] B200 order
   const void* zeros;        // [G, N] biased
@@ -171,11 +175,11 @@ struct W4GemmParams {
   int64_t ldc;
   int M, N, K, group;
   int raw_tma;              // 1: packed tiles by TMA (N % 32 == 0), 0: by the producer warp's lanes
-  int debug;
+  int kb_per_split;         // SWAP kernels launched as clusters: stages per cluster rank (split-K)
 };
 
-constexpr int kW4PackedBytes = 64 * 64;           // 64 k rows x 16 int32 (= 128 output columns)
-constexpr int kW4RawBytes = kW4PackedBytes + 512;  // + the K block's (zero, scale) rows, 256 B each
+constexpr int kW4PackedBytes = 64 * 64;  // one sub-block: 64 k rows x 16 int32 (= 128 output columns)
+constexpr int kW4ZsBytes = 512;          // one sub-block's zero row + scale row, 256 B each
 
 // BM = rows of x per tile (128 or 256); in SWAP mode BM = MT (32 or 64) tokens and the roles of the
 // operands are exchanged: the dequantised weights are the 128-row MN-major A operand, x is the
@@ -183,14 +187,17 @@ constexpr int kW4RawBytes = kW4PackedBytes + 512;  // + the K block's (zero, sca
 template <int BM, bool SWAP>
 struct W4Cfg {
   static constexpr int BN = 128, BK = 64;
-  static constexpr int X_BYTES = BM * 128, B_BYTES = BK * BN * 2;
-  static constexpr int XS = SWAP ? (BM == 32 ? 8 : 6) : (BM == 256 ? 3 : 4);   // x stages
-  static constexpr int BS = SWAP ? 8 : (BM == 256 ? 6 : 7);                    // dequantised stages
-  static constexpr int RAWS = (!SWAP && BM == 256) ? 6 : 8;                    // packed-weight stages
+  static constexpr int KS = (!SWAP && BM == 256) ? 1 : 2;   // 64-row sub-blocks per stage
+  static constexpr int XSUB = BM * 128, BSUB = BK * BN * 2;
+  static constexpr int X_BYTES = KS * XSUB, B_BYTES = KS * BSUB, STAGE_BYTES = X_BYTES + B_BYTES;
+  static constexpr int RAW_BYTES = KS * (kW4PackedBytes + kW4ZsBytes);
+  static constexpr int ST = (!SWAP && BM == 256) ? 4 : 3;   // operand stages
+  static constexpr int RAWS = SWAP ? (BM == 32 ? 10 : BM == 64 ? 8 : 3) : (BM == 256 ? 5 : 3);  // packed stages
   static constexpr int ACC_COLS = BM;  // fp32 columns per accumulator set
   static constexpr int TMEM_COLS = 2 * ACC_COLS < 32 ? 32 : 2 * ACC_COLS;
-  static constexpr int NBARS = 2 * XS + 2 * BS + 2 * RAWS + 4;
-  static constexpr int SMEM = XS * X_BYTES + BS * B_BYTES + RAWS * kW4RawBytes + NBARS * 8 + 16 + 1024;
+  static constexpr int NBARS = 2 * ST + 2 * RAWS + 4;
+  static constexpr int SMEM = ST * STAGE_BYTES + RAWS * RAW_BYTES + NBARS * 8 + 16 + 1024;
+  static_assert(SMEM <= 232448, "shared memory budget");
 };
 
 template <typename T, int BM, bool SWAP, int DQ, int DG>
@@ -199,22 +206,19 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
                   const __grid_constant__ CUtensorMap tmap_z, const __grid_constant__ CUtensorMap tmap_s,
                   const W4GemmParams p) {
   using C = W4Cfg<BM, SWAP>;
-  constexpr int BN = C::BN, BK = C::BK, XS = C::XS, BS = C::BS, RAWS = C::RAWS;
-  constexpr int MH = SWAP ? 1 : BM / 128;          // 128-row x boxes (and accumulators) per stage
+  constexpr int BN = C::BN, BK = C::BK, KS = C::KS, ST = C::ST, RAWS = C::RAWS;
+  constexpr int MH = SWAP ? 1 : BM / 128;          // 128-row x boxes (and accumulators) per sub-block
   constexpr int XBOX = SWAP ? BM : 128;            // rows of one x TMA box
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t b_base = smem_base + XS * C::X_BYTES;
-  const uint32_t raw_base = b_base + BS * C::B_BYTES;
-  const uint32_t bars = raw_base + RAWS * kW4RawBytes;
-  auto xfull_bar = [&](int s) { return bars + 8u * s; };
-  auto xempty_bar = [&](int s) { return bars + 8u * (XS + s); };
-  auto bfull_bar = [&](int s) { return bars + 8u * (2 * XS + s); };
-  auto bempty_bar = [&](int s) { return bars + 8u * (2 * XS + BS + s); };
-  auto rfull_bar = [&](int s) { return bars + 8u * (2 * XS + 2 * BS + s); };
-  auto rempty_bar = [&](int s) { return bars + 8u * (2 * XS + 2 * BS + RAWS + s); };
-  auto tfull_bar = [&](int a) { return bars + 8u * (2 * XS + 2 * BS + 2 * RAWS + a); };
-  auto tempty_bar = [&](int a) { return bars + 8u * (2 * XS + 2 * BS + 2 * RAWS + 2 + a); };
+  const uint32_t raw_base = smem_base + ST * C::STAGE_BYTES;
+  const uint32_t bars = raw_base + RAWS * C::RAW_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (ST + s); };
+  auto rfull_bar = [&](int s) { return bars + 8u * (2 * ST + s); };
+  auto rempty_bar = [&](int s) { return bars + 8u * (2 * ST + RAWS + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * ST + 2 * RAWS + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * ST + 2 * RAWS + 2 + a); };
   const uint32_t tmem_slot = bars + 8u * C::NBARS;
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
@@ -223,19 +227,29 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   const int lane = threadIdx.x & 31;
   const int m_blocks = ceil_div(p.M, BM), n_blocks = ceil_div(p.N, BN);
   const int num_tiles = m_blocks * n_blocks;
-  const int num_kb = ceil_div(p.K, BK);
+  const int num_kb = ceil_div(p.K, BK * KS);       // stages per tile
   const int NC = p.N / 8;
+  const bool zs_rows = (p.group % BK) == 0;        // one (zero, scale) row per sub-block
+  // split-K (SWAP kernels only): a cluster of S CTAs shares one tile, rank r owns stages
+  // [r * kb_per_split, ...); the partial sums meet in the epilogue over distributed shared memory.
+  const uint32_t S = SWAP ? cluster_nctarank() : 1u;
+  const uint32_t crank = SWAP ? cluster_ctarank() : 0u;
+  const int tile0 = S > 1 ? static_cast<int>(blockIdx.x / S) : static_cast<int>(blockIdx.x);
+  const int tile_step = S > 1 ? num_tiles : static_cast<int>(gridDim.x);
+  const int kb_begin = S > 1 ? static_cast<int>(crank) * p.kb_per_split : 0;
+  const int kb_end = S > 1 ? min(num_kb, kb_begin + p.kb_per_split) : num_kb;
+  const int sub_per_group = zs_rows ? p.group / BK : 1;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmap_x);
-    if (p.raw_tma) tc::prefetch_tmap(&tmap_q);
-    for (int s = 0; s < XS; ++s) {
-      tc::mbar_init(xfull_bar(s), 1);
-      tc::mbar_init(xempty_bar(s), 1);
+    if (p.raw_tma) {
+      tc::prefetch_tmap(&tmap_q);
+      tc::prefetch_tmap(&tmap_z);
+      tc::prefetch_tmap(&tmap_s);
     }
-    for (int s = 0; s < BS; ++s) {
-      tc::mbar_init(bfull_bar(s), DQ / DG);  // one arrive per dequant warp of the owning group
-      tc::mbar_init(bempty_bar(s), 1);
+    for (int s = 0; s < ST; ++s) {
+      tc::mbar_init(full_bar(s), 1 + DQ / DG);  // TMA expect_tx arrive + the owning group's warps
+      tc::mbar_init(empty_bar(s), 1);
     }
     for (int s = 0; s < RAWS; ++s) {
       tc::mbar_init(rfull_bar(s), 1);
@@ -261,18 +275,18 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         const int m_blk = tile % m_blocks;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          tc::mbar_wait(xempty_bar(stage), phase ^ 1u);
-          if (p.debug & 8) { tc::mbar_arrive(xfull_bar(stage)); } else {
-          tc::mbar_arrive_expect_tx(xfull_bar(stage), C::X_BYTES);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          tc::mbar_wait(empty_bar(stage), phase ^ 1u);
+          tc::mbar_arrive_expect_tx(full_bar(stage), C::X_BYTES);
 #pragma unroll
-          for (int h = 0; h < MH; ++h)
-            tc::tma_load_2d(smem_base + stage * C::X_BYTES + h * (128 * 128), &tmap_x,
-                            xfull_bar(stage), kb * BK, m_blk * BM + h * XBOX);
-          }
-          if (++stage == XS) {
+          for (int j = 0; j < KS; ++j)
+#pragma unroll
+            for (int h = 0; h < MH; ++h)
+              tc::tma_load_2d(smem_base + stage * C::STAGE_BYTES + (j * MH + h) * (XBOX * 128),
+                              &tmap_x, full_bar(stage), (kb * KS + j) * BK, m_blk * BM + h * XBOX);
+          if (++stage == ST) {
             stage = 0;
             phase ^= 1u;
           }
@@ -280,61 +294,58 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       }
     }
   } else if (warp == 6 + DQ) {
-    // ===================== producer of the packed-weight ring =====================
-    // Every stage also carries the K block's (zero, scale) rows (group sizes that are a multiple of
-    // the K block): the dequant warps then touch shared memory only, so the MEMBAR that
-    // fence.proxy.async implies never waits on a global load.
-    const bool zs_rows = (p.group % BK) == 0;
-    const int kb_per_group = zs_rows ? p.group / BK : 1;
+    // ===================== producer of the packed ring =====================
     int rs = 0;
     uint32_t rphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
       const int n_blk = tile / m_blocks;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const uint32_t dst = raw_base + rs * kW4RawBytes;
-        const int g = kb / kb_per_group;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        const uint32_t dst = raw_base + rs * C::RAW_BYTES;
+        const uint32_t zdst = dst + KS * kW4PackedBytes;
         if (p.raw_tma) {
           if (lane == 0) {
             tc::mbar_wait(rempty_bar(rs), rphase ^ 1u);
-            if (p.debug & 4) { tc::mbar_arrive(rfull_bar(rs)); } else {
-            tc::mbar_arrive_expect_tx(rfull_bar(rs), zs_rows ? kW4RawBytes : kW4PackedBytes);
-            if (p.raw_tma == 2) {  // EXPERIMENT: tile-major packed weights, one 4 KiB bulk copy
-              const char* src = reinterpret_cast<const char*>(p.qweight) +
-                                (static_cast<int64_t>(n_blk) * num_kb + kb) * kW4PackedBytes;
-              asm volatile(
-                  "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
-                  "l"(src), "r"(kW4PackedBytes), "r"(rfull_bar(rs))
-                  : "memory");
-            } else
-            tc::tma_load_2d_hint(dst, &tmap_q, rfull_bar(rs), n_blk * (BN / 8), kb * BK,
+            tc::mbar_arrive_expect_tx(rfull_bar(rs),
+                                      KS * (kW4PackedBytes + (zs_rows ? kW4ZsBytes : 0)));
+            tc::tma_load_2d_hint(dst, &tmap_q, rfull_bar(rs), n_blk * (BN / 8), kb * KS * BK,
                                  m_blocks > 1 ? tc::kEvictLast : tc::kEvictFirst);
             if (zs_rows) {
-              tc::tma_load_2d(dst + kW4PackedBytes, &tmap_z, rfull_bar(rs), n_blk * BN, g);
-              tc::tma_load_2d(dst + kW4PackedBytes + 256, &tmap_s, rfull_bar(rs), n_blk * BN, g);
-            }
+#pragma unroll
+              for (int j = 0; j < KS; ++j) {
+                const int g = (kb * KS + j) / sub_per_group;  // past the last group: TMA zero fill
+                tc::tma_load_2d(zdst + j * kW4ZsBytes, &tmap_z, rfull_bar(rs), n_blk * BN, g);
+                tc::tma_load_2d(zdst + j * kW4ZsBytes + 256, &tmap_s, rfull_bar(rs), n_blk * BN, g);
+              }
             }
           }
         } else {
           // rows whose pitch is not a multiple of 16 bytes: the 32 lanes copy the tile word by word
           tc::mbar_wait(rempty_bar(rs), rphase ^ 1u);
-          uint32_t v[32];
+#pragma unroll 1
+          for (int j = 0; j < KS; ++j) {
+            uint32_t v[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int w = i * 32 + lane, r = w >> 4, cc = n_blk * (BN / 8) + (w & 15);
-            const int k = kb * BK + r;
-            v[i] = (k < p.K && cc < NC) ? __ldg(p.qweight + static_cast<int64_t>(k) * NC + cc) : 0u;
-          }
+            for (int i = 0; i < 32; ++i) {
+              const int w = i * 32 + lane, r = w >> 4, cc = n_blk * (BN / 8) + (w & 15);
+              const int k = (kb * KS + j) * BK + r;
+              v[i] = (k < p.K && cc < NC) ? __ldg(p.qweight + static_cast<int64_t>(k) * NC + cc) : 0u;
+            }
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst + (i * 32 + lane) * 4), "r"(v[i])
-                         : "memory");
-          if (zs_rows) {  // lanes 0..15: zeros, 16..31: scales, 8 columns (16 bytes) each
-            const int cc = n_blk * (BN / 8) + (lane & 15);
-            const uint4* src = static_cast<const uint4*>(lane < 16 ? p.zeros : p.scales);
-            const uint4 zs = cc < NC ? __ldg(src + static_cast<int64_t>(g) * NC + cc) : make_uint4(0, 0, 0, 0);
-            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + kW4PackedBytes + lane * 16),
-                         "r"(zs.x), "r"(zs.y), "r"(zs.z), "r"(zs.w)
-                         : "memory");
+            for (int i = 0; i < 32; ++i)
+              asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst + j * kW4PackedBytes + (i * 32 + lane) * 4),
+                           "r"(v[i])
+                           : "memory");
+            if (zs_rows) {  // lanes 0..15: zeros, 16..31: scales, 8 columns (16 bytes) each
+              const int cc = n_blk * (BN / 8) + (lane & 15);
+              const int g = (kb * KS + j) / sub_per_group;
+              const uint4* src = static_cast<const uint4*>(lane < 16 ? p.zeros : p.scales);
+              const uint4 zs = (cc < NC && static_cast<int64_t>(g) * p.group < p.K)
+                                   ? __ldg(src + static_cast<int64_t>(g) * NC + cc)
+                                   : make_uint4(0, 0, 0, 0);
+              asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(zdst + j * kW4ZsBytes + lane * 16),
+                           "r"(zs.x), "r"(zs.y), "r"(zs.z), "r"(zs.w)
+                           : "memory");
+            }
           }
           __syncwarp();
           if (lane == 0) tc::mbar_arrive(rfull_bar(rs));
@@ -353,44 +364,42 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       // swap  : A = weights (MN-major, M = 128 output columns), B = x (K-major, N = MT tokens)
       constexpr uint32_t idesc = SWAP ? tc::make_idesc(fmt, fmt, 128, BM, 1, 0)
                                       : tc::make_idesc(fmt, fmt, 128, BN, 0, 1);
-      int xs = 0, bs = 0;
-      uint32_t xphase = 0, bphase = 0;
+      int stage = 0;
+      uint32_t phase = 0;
       int local = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_step, ++local) {
         const int acc = local & 1;
         tc::mbar_wait(tempty_bar(acc), ((local >> 1) & 1u) ^ 1u);
         tc::tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * C::ACC_COLS;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          tc::mbar_wait(xfull_bar(xs), xphase);
-          tc::mbar_wait(bfull_bar(bs), bphase);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          tc::mbar_wait(full_bar(stage), phase);
           tc::tc_fence_after();
-          const uint32_t sx = smem_base + xs * C::X_BYTES;
-          const uint32_t sw = b_base + bs * C::B_BYTES;
+          const uint32_t sx = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sw = sx + C::X_BYTES;
 #pragma unroll
-          for (int kk = 0; kk < BK / 16; ++kk) {
-            // weight rows kk*16.. of the [64 k x 128 n] tile; panels of 64 n are 64*128 bytes apart
-            const uint64_t wdesc = tc::make_smem_desc_sw128(sw + kk * 16 * 128, 1024, BK * 128);
+          for (int j = 0; j < KS; ++j) {
 #pragma unroll
-            for (int h = 0; h < MH; ++h) {
-              const uint64_t xdesc =
-                  tc::make_smem_desc_sw128(sx + h * (128 * 128) + kk * 32, 1024, 16);
-              if (p.debug & 2) continue;
-              if (SWAP)
-                tc::mma_f16(tmem_d, wdesc, xdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
-              else
-                tc::mma_f16(tmem_d + h * BN, xdesc, wdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            for (int kk = 0; kk < BK / 16; ++kk) {
+              // weight rows kk*16.. of a [64 k x 128 n] sub-tile; panels of 64 n are 64*128 B apart
+              const uint64_t wdesc =
+                  tc::make_smem_desc_sw128(sw + j * C::BSUB + kk * 16 * 128, 1024, BK * 128);
+#pragma unroll
+              for (int h = 0; h < MH; ++h) {
+                const uint64_t xdesc = tc::make_smem_desc_sw128(
+                    sx + (j * MH + h) * (XBOX * 128) + kk * 32, 1024, 16);
+                const uint32_t accum = ((kb - kb_begin) | j | kk) != 0 ? 1u : 0u;
+                if (SWAP)
+                  tc::mma_f16(tmem_d, wdesc, xdesc, idesc, accum);
+                else
+                  tc::mma_f16(tmem_d + h * BN, xdesc, wdesc, idesc, accum);
+              }
             }
           }
-          tc::mma_commit(xempty_bar(xs));
-          tc::mma_commit(bempty_bar(bs));
-          if (++xs == XS) {
-            xs = 0;
-            xphase ^= 1u;
-          }
-          if (++bs == BS) {
-            bs = 0;
-            bphase ^= 1u;
+          tc::mma_commit(empty_bar(stage));
+          if (++stage == ST) {
+            stage = 0;
+            phase ^= 1u;
           }
         }
         tc::mma_commit(tfull_bar(acc));
@@ -402,29 +411,69 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     T* out = static_cast<T*>(p.out);
     const T* bias = static_cast<const T*>(p.bias);
     int local = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step, ++local) {
       const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
       const int acc = local & 1;
       tc::mbar_wait(tfull_bar(acc), (local >> 1) & 1u);
       tc::tc_fence_after();
       if (SWAP) {
         // accumulator lanes = output columns, TMEM columns = tokens
-        const int n = n_blk * BN + quarter * 32 + lane;
+        const int ch = quarter * 32 + lane;
+        const int n = n_blk * BN + ch;
         const float bv = (bias && n < p.N) ? to_float<T>(bias[n]) : 0.f;
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * C::ACC_COLS;
+        if (S == 1) {
 #pragma unroll 1
-        for (int c = 0; c < BM / 32; ++c) {
-          if (c * 32 >= p.M) break;
-          uint32_t r[32];
-          tc::tmem_ld32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) +
-                            acc * C::ACC_COLS + c * 32,
-                        r);
-          tc::tmem_ld_wait();
-          if (n < p.N) {
+          for (int c = 0; c < BM / 32; ++c) {
+            if (c * 32 >= p.M) break;
+            uint32_t r[32];
+            tc::tmem_ld32(lane_addr + c * 32, r);
+            tc::tmem_ld_wait();
+            if (n < p.N) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const int m = c * 32 + j;
+                if (m < p.M) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(__uint_as_float(r[j]) + bv);
+              }
+            }
+          }
+        } else {
+          // fixed-order cluster reduction (same scheme as fp8_gemm_smallm.cuh): after barrier 1 every
+          // peer's operand ring is idle; token m of my partial is pushed to rank m % S, slot
+          // [my rank][m / S][channel] of ITS ring; after barrier 2 each rank sums the S slots of its
+          // own tokens from local shared memory in rank order (deterministic) and stores.
+          const int tpr = ceil_div(p.M, static_cast<int>(S));
+          const uint32_t push_base = smem_base + (crank * tpr * 128 + ch) * 4;
+          __syncwarp();
+          cluster_sync_all();  // barrier 1
+          uint32_t dst_rank = 0, dst_slot = 0;
+#pragma unroll 1
+          for (int c = 0; c < BM / 32; ++c) {
+            if (c * 32 >= p.M) break;
+            uint32_t r[32];
+            tc::tmem_ld32(lane_addr + c * 32, r);
+            tc::tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              const int m = c * 32 + j;
-              if (m < p.M) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(__uint_as_float(r[j]) + bv);
+              if (c * 32 + j < p.M) {
+                const uint32_t a = map_to_rank(push_base + dst_slot * 512, dst_rank);
+                asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(a), "f"(__uint_as_float(r[j])) : "memory");
+                if (++dst_rank == S) {
+                  dst_rank = 0;
+                  ++dst_slot;
+                }
+              }
             }
+          }
+          __syncwarp();
+          cluster_sync_all();  // barrier 2: every peer's pushes into my ring are visible
+          const float* part = reinterpret_cast<const float*>(smem_raw + (smem_base - smem_u32(smem_raw))) + ch;
+          int m = static_cast<int>(crank);
+          for (int j = 0; j < tpr; ++j, m += S) {
+            if (m >= p.M) break;
+            float sum = 0.f;
+            for (uint32_t q = 0; q < S; ++q) sum += part[(q * tpr + j) * 128];
+            if (n < p.N) out[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(sum + bv);
           }
         }
       } else
@@ -476,56 +525,56 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       if (lane == 0) tc::mbar_arrive(tempty_bar(acc));
     }
   } else {
-    // ===================== dequant warps (6..6+DQ-1): packed ring -> 16-bit swizzled B stage ======
-    // The warps form DG groups; group j owns every DG-th K block of this CTA's K-block sequence
-    // (the sequence runs on across tiles), so the fixed per-block latency chain of one warp (barrier
-    // polls, ld.shared, fence.proxy.async) overlaps with the other groups' blocks.
+    // ===================== dequant warps (6..6+DQ-1): packed ring -> 16-bit swizzled weight tile ====
+    // The warps form DG groups; group j owns every DG-th stage of this CTA's stage sequence (the
+    // sequence runs on across tiles), so the latency chain of one group's stage (barrier polls,
+    // ld.shared, fence.proxy.async) overlaps with the other groups' stages.
     constexpr int NT = (DQ / DG) * 32;    // threads per group
-    constexpr int RSTEP = NT / 16;        // row stride of one thread's rows inside a K block
-    constexpr int RPT = BK / RSTEP;       // rows per thread per K block
+    constexpr int RSTEP = NT / 16;        // row stride of one thread's rows inside a sub-block
+    constexpr int RPT = BK / RSTEP;       // rows per thread per sub-block
     static_assert(DQ % DG == 0 && RSTEP % 8 == 0, "the swizzle term must not depend on the row index i");
-    static_assert(DG <= BS && DG <= RAWS, "a group advances its ring position by DG with one wrap");
+    static_assert(DG <= ST && DG <= RAWS, "a group advances its ring position by DG with one wrap");
     const int grp = (warp - 6) / (DQ / DG);
     const int t = threadIdx.x - 6 * 32 - grp * NT;
     const int col = t & 15;               // int32 column inside the 128-wide n tile
     const int row0 = t >> 4;              // rows row0 + RSTEP * i
     const uint4* zeros = static_cast<const uint4*>(p.zeros);    // rows of NC uint4 (8 columns each)
     const uint4* scales = static_cast<const uint4*>(p.scales);
-    const bool group_fast = (p.group % BK) == 0;  // one (zero, scale) row per K block
-    // byte offset of this thread's 16-byte chunk of row row0 inside a B stage; rows row0 + RSTEP*i
-    // keep the same swizzle term because RSTEP is a multiple of 8
-    const uint32_t b_off = (col >> 3) * (BK * 128) + row0 * 128 + (((col & 7) ^ (row0 & 7)) << 4);
+    // byte offset of this thread's 16-byte chunk of row row0 inside a weight sub-tile; rows
+    // row0 + RSTEP*i keep the same swizzle term because RSTEP is a multiple of 8
+    const uint32_t b_off =
+        C::X_BYTES + (col >> 3) * (BK * 128) + row0 * 128 + (((col & 7) ^ (row0 & 7)) << 4);
     const uint32_t r_off = row0 * 64 + col * 4;
-    int stage = grp, rs = grp;            // ring positions of this group's next K block
+    int stage = grp, rs = grp;            // ring positions of this group's next stage
     uint32_t phase = 0, rphase = 0;
-    int tile = blockIdx.x, kb = grp;
-    bool new_tile = true;
-    int cc = 0;
+    int tile = tile0, kb = kb_begin + grp;
     while (true) {
-      while (kb >= num_kb) {
-        kb -= num_kb;
-        tile += gridDim.x;
-        new_tile = true;
+      while (kb >= kb_end) {
+        kb -= kb_end - kb_begin;
+        tile += tile_step;
       }
       if (tile >= num_tiles) break;
-      if (new_tile) {
-        const int c = (tile / m_blocks) * (BN / 8) + col;  // global int32 column
-        cc = c < NC ? c : NC - 1;  // clamped: columns >= N are computed but never stored
-        new_tile = false;
-      }
       tc::mbar_wait(rfull_bar(rs), rphase);
-      const uint32_t rsrc = raw_base + rs * kW4RawBytes + r_off;
-      uint32_t q[RPT];
+      const uint32_t rsrc = raw_base + rs * C::RAW_BYTES;
+      uint32_t q[KS][RPT];
+      uint4 zb[KS], sc[KS];
 #pragma unroll
-      for (int i = 0; i < RPT; ++i)
-        asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(q[i]) : "r"(rsrc + RSTEP * i * 64));
-      uint4 zb = make_uint4(0, 0, 0, 0), sc = zb;
-      if (group_fast) {  // this K block's (zero, scale) rows travel with the packed tile
-        const uint32_t zsrc = raw_base + rs * kW4RawBytes + kW4PackedBytes + col * 16;
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
-                     : "=r"(zb.x), "=r"(zb.y), "=r"(zb.z), "=r"(zb.w) : "r"(zsrc));
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
-                     : "=r"(sc.x), "=r"(sc.y), "=r"(sc.z), "=r"(sc.w) : "r"(zsrc + 256));
+      for (int j = 0; j < KS; ++j) {
+#pragma unroll
+        for (int i = 0; i < RPT; ++i)
+          asm volatile("ld.shared.u32 %0, [%1];\n"
+                       : "=r"(q[j][i])
+                       : "r"(rsrc + j * kW4PackedBytes + r_off + RSTEP * i * 64));
+        zb[j] = sc[j] = make_uint4(0, 0, 0, 0);
+        if (zs_rows) {  // the sub-block's (zero, scale) rows travel with the packed tile
+          const uint32_t zsrc = rsrc + KS * kW4PackedBytes + j * kW4ZsBytes + col * 16;
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                       : "=r"(zb[j].x), "=r"(zb[j].y), "=r"(zb[j].z), "=r"(zb[j].w)
+                       : "r"(zsrc));
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                       : "=r"(sc[j].x), "=r"(sc[j].y), "=r"(sc[j].z), "=r"(sc[j].w)
+                       : "r"(zsrc + 256));
+        }
       }
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(rempty_bar(rs));
@@ -534,52 +583,69 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         rs -= RAWS;
         rphase ^= 1u;
       }
-      const uint32_t dst = b_base + stage * C::B_BYTES + b_off;
-      if (group_fast) {
+      const uint32_t dst = smem_base + stage * C::STAGE_BYTES + b_off;
+      if (zs_rows) {
         uint4 w[RPT];
 #pragma unroll
-        for (int i = 0; i < RPT; ++i) w[i] = dequant8<T>(q[i], zb, sc);
-        tc::mbar_wait(bempty_bar(stage), phase ^ 1u);
-        if (!(p.debug & 1))
+        for (int i = 0; i < RPT; ++i) w[i] = dequant8<T>(q[0][i], zb[0], sc[0]);
+        tc::mbar_wait(empty_bar(stage), phase ^ 1u);
 #pragma unroll
-        for (int i = 0; i < RPT; ++i)
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + RSTEP * i * 128),
-                       "r"(w[i].x), "r"(w[i].y), "r"(w[i].z), "r"(w[i].w)
-                       : "memory");
-      } else {
-        // groups smaller than / not aligned to a K block: look the group up per row
-        int g_cached = -1;
-        tc::mbar_wait(bempty_bar(stage), phase ^ 1u);
+        for (int j = 0; j < KS; ++j) {
 #pragma unroll
-        for (int i = 0; i < RPT; ++i) {
-          const int k = kb * BK + row0 + RSTEP * i;
-          uint4 w = make_uint4(0, 0, 0, 0);
-          if (k < p.K) {  // rows past K must be exact zeros (x is zero-filled there, 0 * garbage != 0)
-            const int g = k / p.group;
-            if (g != g_cached) {
-              g_cached = g;
-              zb = __ldg(zeros + static_cast<int64_t>(g) * NC + cc);
-              sc = __ldg(scales + static_cast<int64_t>(g) * NC + cc);
-            }
-            w = dequant8<T>(q[i], zb, sc);
+          for (int i = 0; i < RPT; ++i)
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + j * C::BSUB + RSTEP * i * 128),
+                         "r"(w[i].x), "r"(w[i].y), "r"(w[i].z), "r"(w[i].w)
+                         : "memory");
+          if (j + 1 < KS) {
+#pragma unroll
+            for (int i = 0; i < RPT; ++i) w[i] = dequant8<T>(q[(j + 1) % KS][i], zb[(j + 1) % KS], sc[(j + 1) % KS]);
           }
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + RSTEP * i * 128),
-                       "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w)
-                       : "memory");
+        }
+      } else {
+        // groups smaller than / not aligned to a sub-block: look the group up per row
+        const int c = (tile / m_blocks) * (BN / 8) + col;  // global int32 column
+        const int cc = c < NC ? c : NC - 1;  // clamped: columns >= N are computed but never stored
+        int g_cached = -1;
+        uint4 zg = make_uint4(0, 0, 0, 0), sg = zg;
+        tc::mbar_wait(empty_bar(stage), phase ^ 1u);
+#pragma unroll
+        for (int j = 0; j < KS; ++j) {
+#pragma unroll
+          for (int i = 0; i < RPT; ++i) {
+            const int k = (kb * KS + j) * BK + row0 + RSTEP * i;
+            uint4 w = make_uint4(0, 0, 0, 0);
+            if (k < p.K) {  // rows past K must be exact zeros (x is zero-filled there, 0 * garbage != 0)
+              const int g = k / p.group;
+              if (g != g_cached) {
+                g_cached = g;
+                zg = __ldg(zeros + static_cast<int64_t>(g) * NC + cc);
+                sg = __ldg(scales + static_cast<int64_t>(g) * NC + cc);
+              }
+              w = dequant8<T>(q[j][i], zg, sg);
+            }
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst + j * C::BSUB + RSTEP * i * 128),
+                         "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w)
+                         : "memory");
+          }
         }
       }
-      if (!(p.debug & 16)) tc::fence_proxy_async_smem();
+      tc::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(bfull_bar(stage));
+      if (lane == 0) tc::mbar_arrive(full_bar(stage));
       stage += DG;
-      if (stage >= BS) {
-        stage -= BS;
+      if (stage >= ST) {
+        stage -= ST;
         phase ^= 1u;
       }
       kb += DG;
     }
   }
 
+  if (SWAP && S > 1 && (warp < 2 || warp >= 6)) {  // everyone but the epilogue warps (done above)
+    __syncwarp();
+    cluster_sync_all();
+    cluster_sync_all();
+  }
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
@@ -587,17 +653,18 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
 // Tile selection.  M <= 64: swap-AB (tokens are the UMMA N dimension).  Otherwise 128-row tiles, or
 // 256-row tiles (half the dequant work per flop) once they still fill the machine.
-// B200_W4_BM=32|64 (swap) |128|256 overrides (sweeps).
+// B200_W4_BM=32|64|129 (swap) |128|256 overrides (sweeps).
 static int w4_pick_bm(int M, int N, int sms) {
   static int forced = [] {
     const char* v = std::getenv("B200_W4_BM");
     return v && *v ? std::atoi(v) : 0;
   }();
   if ((forced == 32 || forced == 64) && M <= forced) return forced;
+  if (forced == 129 && M <= 128) return forced;
   if (forced == 128 || forced == 256) return forced;
   if (M <= 32) return 32;
   if (M <= 64) return 64;
-  if (M <= 128) return 128;
+  if (M <= 128) return ceil_div(N, 128) <= 64 ? 129 : 128;  // 129 = swap-AB with 128 tokens (split-K)
   return ceil_div(M, 256) * ceil_div(N, 128) >= (sms * 3) / 4 ? 256 : 128;
 }
 
@@ -608,12 +675,9 @@ static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStr
   int rc = make_tmap_2d(&tx, x, p.M, p.K, ldx * 2, SWAP ? BM : 128, 64, 2, false);
   if (rc) return rc;
   p.raw_tma = (p.N % 32 == 0 && aligned16(p.qweight)) ? 1 : 0;
-  {
-    static const int tiled = [] { const char* v = std::getenv("B200_W4_TILED"); return v && *v ? std::atoi(v) : 0; }();
-    if (tiled && p.raw_tma && p.N % 128 == 0 && p.K % 64 == 0) p.raw_tma = 2;
-  }
   if (p.raw_tma) {
-    rc = make_tmap_2d_plain(&tq, p.qweight, p.K, p.N / 8, static_cast<uint64_t>(p.N / 8) * 4, 64, 16, 4);
+    rc = make_tmap_2d_plain(&tq, p.qweight, p.K, p.N / 8, static_cast<uint64_t>(p.N / 8) * 4,
+                            C::KS * 64, 16, 4);
     if (rc) return rc;
   } else {
     tq = tx;
@@ -634,9 +698,35 @@ static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStr
   }
   const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, 128);
   const int sms = device_sm_count();
+  // split-K for the swap-AB kernels when the tiles alone leave most SMs idle: the largest power of
+  // two S <= 8 with tiles * S <= SMs and at least two stages per rank.  B200_W4_SPLITS forces it.
+  int S = 1;
+  if (SWAP) {
+    static const int forced = [] {
+      const char* v = std::getenv("B200_W4_SPLITS");
+      return v && *v ? std::atoi(v) : 0;
+    }();
+    const int num_kb = ceil_div(p.K, 64 * C::KS);
+    if (forced > 0) {
+      S = forced;
+    } else {
+      // clusters are placed inside one GPC (16-20 SMs): S CTAs x tiles must fit 8 GPCs in one wave
+      for (int c = 8; c >= 2; --c)
+        if (tiles <= 8 * (16 / c) && num_kb >= 4 * c) {
+          S = c;
+          break;
+        }
+    }
+    while (S > 1 && (S - 1) * ceil_div(num_kb, S) >= num_kb) --S;
+    p.kb_per_split = ceil_div(num_kb, S);
+  }
   {
     ScopedKernelTimer timer("w4a16_gemm", st);
-    kern<<<tiles < sms ? tiles : sms, (7 + DQ) * 32, C::SMEM, st>>>(tx, tq, tz, ts, p);
+    if (S > 1) {
+      B200_CUDA_OK(launch_kernel(kern, dim3(tiles * S), dim3((7 + DQ) * 32), C::SMEM, st, S, 0, tx, tq, tz, ts, p));
+    } else {
+      kern<<<tiles < sms ? tiles : sms, (7 + DQ) * 32, C::SMEM, st>>>(tx, tq, tz, ts, p);
+    }
   }
   B200_CHECK_LAUNCH("w4a16_gemm_kernel");
   return 0;
@@ -716,7 +806,7 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
                "b200_w4a16_gemm: x/zeros/scales must be 16-byte aligned, ldx %% 8 == 0");
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, "b200_w4a16_gemm: dtype %d", dtype);
   // decode regime: HBM-bound GEMV on the packed weights (w4a16_gemv.cu)
-  if (M <= w4a16_gemv_max_m() && w4a16_gemv_supported(M, N, K, group_size) && aligned16(qweight))
+  if (M <= w4a16_gemv_max_m(N) && w4a16_gemv_supported(M, N, K, group_size) && aligned16(qweight))
     return b200_w4a16_gemv(x, ldx, qweight, zeros, scales, bias, out, ldc, M, N, K, group_size,
                            dtype, stream);
   W4GemmParams p;
@@ -732,25 +822,21 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
   p.group = group_size;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   p.raw_tma = 0;
-  {
-    static const int dbg = [] { const char* v = std::getenv("B200_W4_DEBUG"); return v && *v ? std::atoi(v) : 0; }();
-    p.debug = dbg;
-  }
+  p.kb_per_split = 0;
   const int bm = w4_pick_bm(M, N, device_sm_count());
-  // dequant warp layout: DQ warps in DG groups that own alternate K blocks.  B200_W4_CFG: 0 = 8 warps /
-  // 1 group, 1 = 8 / 2 (default), 2 = 16 / 4 (16 / 2 for the 256-row tile, whose ring has 3 stages)
+  // dequant warp layout: 8 warps in DG groups that own alternate stages.  B200_W4_CFG: 0 = one
+  // group, 1 = two groups (default)
   static const int cfg = [] {
     const char* v = std::getenv("B200_W4_CFG");
     return v && *v ? std::atoi(v) : 1;
   }();
-#define B200_W4_LAUNCH_C(TT, DQ_, DG_, DG256_)                                          \
-  (bm == 256  ? launch_w4a16_gemm<TT, 256, false, DQ_, DG256_>(x, ldx, p, st)           \
+#define B200_W4_LAUNCH_C(TT, DQ_, DG_)                                                  \
+  (bm == 256  ? launch_w4a16_gemm<TT, 256, false, DQ_, DG_>(x, ldx, p, st)              \
    : bm == 128 ? launch_w4a16_gemm<TT, 128, false, DQ_, DG_>(x, ldx, p, st)             \
+   : bm == 129 ? launch_w4a16_gemm<TT, 128, true, DQ_, DG_>(x, ldx, p, st)              \
    : bm == 64  ? launch_w4a16_gemm<TT, 64, true, DQ_, DG_>(x, ldx, p, st)               \
                : launch_w4a16_gemm<TT, 32, true, DQ_, DG_>(x, ldx, p, st))
-#define B200_W4_LAUNCH(TT)                                                              \
-  (cfg == 0 ? B200_W4_LAUNCH_C(TT, 8, 1, 1)                                             \
-   : cfg == 2 ? B200_W4_LAUNCH_C(TT, 16, 4, 2) : B200_W4_LAUNCH_C(TT, 8, 2, 2))
+#define B200_W4_LAUNCH(TT) (cfg == 0 ? B200_W4_LAUNCH_C(TT, 8, 1) : B200_W4_LAUNCH_C(TT, 8, 2))
   return dtype == B200_F16 ? B200_W4_LAUNCH(__half) : B200_W4_LAUNCH(__nv_bfloat16);
 #undef B200_W4_LAUNCH_C
 #undef B200_W4_LAUNCH

@@ -329,15 +329,21 @@ w4a16_gemv_kernel(const GemvParams p) {
 static std::atomic<int> g_gemv_max_m{-1};
 static std::atomic<int> g_gemv_splits{-1};
 
-int w4a16_gemv_max_m() {
+// Largest M the dispatch in b200_w4a16_gemm hands to the GEMV for an N-column weight.  Explicit
+// settings (b200_w4a16_gemv_config / B200_W4A16_GEMV_MAX_M) win.  Default, from the cfg-4 sweep
+// (profiles/r01_bench_w4a16_crossover.json): the swap-AB split-K tcgen05 kernel is as fast or faster
+// from M = 1 on every shape whose tiles can be split over a cluster (N / 128 <= 64); the GEMV keeps
+// M <= 2 on the wide gate_up weights, which fill the machine without split-K.
+int w4a16_gemv_max_m(int N) {
   int v = g_gemv_max_m.load(std::memory_order_relaxed);
   if (v < 0) {
-    const char* e = std::getenv("B200_W4A16_GEMV_MAX_M");
-    v = (e && *e) ? std::atoi(e) : 16;
-    if (v > 16) v = 16;
-    g_gemv_max_m.store(v, std::memory_order_relaxed);
+    static const int env = [] {
+      const char* e = std::getenv("B200_W4A16_GEMV_MAX_M");
+      return (e && *e) ? std::atoi(e) : -1;
+    }();
+    v = env >= 0 ? env : (N / 128 > 64 ? 2 : 0);
   }
-  return v;
+  return v > 16 ? 16 : v;
 }
 
 bool w4a16_gemv_supported(int M, int N, int K, int group) {

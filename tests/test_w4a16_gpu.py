@@ -71,7 +71,7 @@ def _awq_layer(k, n, group, dtype, seed, realistic=False):
             _rand_i32((k // group, n // 8), seed + 1))
 
 
-@pytest.mark.parametrize("m", [1, 16, 24, 64, 130, 1024])
+@pytest.mark.parametrize("m", [1, 16, 24, 64, 100, 130, 1024])
 @pytest.mark.parametrize("k,n,group", [(512, 256, 128), (5120, 3584, 128), (2560, 5120, 128),
                                        (256, 136, 32), (1024, 1000, 64)])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
