@@ -5,11 +5,11 @@
 //   C[m,n] = sum_kb ( A[m, kb] . B[n, kb]^T ) * As[m, kb] * Bs[n/128, kb]      (fp32), then cast
 //
 // The fp32 scales differ per 128-wide K block, so they cannot ride inside one tensor-core
-// accumulation.  Each K block is therefore multiplied into a FRESH TMEM accumulator (4 rotating
-// 128-column buffers); the four epilogue warps pull the finished partial tile out of TMEM and
+// accumulation.  Each K block is therefore multiplied into a FRESH TMEM accumulator (2 rotating
+// 256-column buffers); the eight epilogue warps pull the finished partial tile out of TMEM and
 // "promote" it into fp32 registers with one packed FMA per element pair:
 //   acc[m, :] += (As[m,kb] * Bs[nb,kb]) * partial[m, :]
-// (BLOCK_N = 128 = one weight scale block, so the combined scale is a per-thread scalar) while
+// (a warpgroup owns 128 columns = one weight scale block, so the combined scale is a per-thread scalar) while
 // the MMA warp already works on the next K blocks.  Same TMA / mbarrier ring as gemm_tc.cuh.
 #include "fp8_gemm_smallm.cuh"
 
@@ -26,15 +26,28 @@ struct BlockGemmParams {
   int M, N, K;
 };
 
-constexpr int kBlkStages = 6;
-constexpr int kBlkBufs = 4;   // TMEM accumulator buffers of 128 columns
+// Tile 128 x 256: a 128 x 128 tile moves 64 KiB through shared memory (TMA in + UMMA out) per 256
+// tensor-core clocks, twice what an SM's shared memory delivers, and plateaued at 1.59 PFLOP/s
+// whatever the epilogue did (measured).  With N = 256 the tile spans TWO weight scale blocks: two
+// epilogue warpgroups take one 128-column block each, so the combined scale stays a per-thread
+// scalar.  One K block (512 tensor-core clocks) per TMEM hand-off, two 256-column accumulators.
+// BN = 128 (twice the tiles, each warpgroup takes 64 columns of the one scale block) is kept for
+// problems whose 128 x 256 tiles would leave SMs idle.
+constexpr int kBlkThreads = 320;  // TMA, MMA, 2 x 4 epilogue warps
+template <int BN>
+struct BlkCfg {
+  static constexpr int STAGES = BN == 256 ? 4 : 6;   // 48 / 32 KiB each: A 128 x 128, B BN x 128
+  static constexpr int NBUF = 512 / BN;              // TMEM accumulator buffers of BN columns
+  static constexpr int SMEM = STAGES * (128 + BN) * 128 + (2 * STAGES + 2 * NBUF) * 8 + 16 + 1024;
+};
 
-template <typename OutT>
-__global__ void __launch_bounds__(192, 1)
+template <typename OutT, int BN>
+__global__ void __launch_bounds__(kBlkThreads, 1)
 fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                       const __grid_constant__ CUtensorMap tmap_b, const BlockGemmParams p) {
-  constexpr int BLOCK = 128, STAGES = kBlkStages, NBUF = kBlkBufs;
-  constexpr int A_BYTES = BLOCK * 128, STAGE_BYTES = 2 * A_BYTES;
+  constexpr int BLOCK = 128, STAGES = BlkCfg<BN>::STAGES, NBUF = BlkCfg<BN>::NBUF;
+  constexpr int COLS = BN / 2;  // columns per epilogue warpgroup
+  constexpr int A_BYTES = BLOCK * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = smem_base + STAGES * STAGE_BYTES;
@@ -48,7 +61,7 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int m_blocks = ceil_div(p.M, BLOCK), n_blocks = ceil_div(p.N, BLOCK);
+  const int m_blocks = ceil_div(p.M, BLOCK), n_blocks = ceil_div(p.N, BN);
   const int num_tiles = m_blocks * n_blocks;
   const int num_kb = ceil_div(p.K, BLOCK);
 
@@ -61,12 +74,12 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int a = 0; a < NBUF; ++a) {
       tc::mbar_init(tfull_bar(a), 1);
-      tc::mbar_init(tempty_bar(a), 4);
+      tc::mbar_init(tempty_bar(a), 8);
     }
     tc::fence_barrier_init();
   }
   if (warp == 1) {
-    tc::tmem_alloc(tmem_slot, NBUF * BLOCK);
+    tc::tmem_alloc(tmem_slot, NBUF * BN);
     tc::tmem_relinquish();
   }
   tc::tc_fence_before();
@@ -87,7 +100,7 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc::mbar_arrive_expect_tx(full_bar(stage), STAGE_BYTES);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * BLOCK, m_blk * BLOCK);
-          tc::tma_load_2d(sa + A_BYTES, &tmap_b, full_bar(stage), kb * BLOCK, n_blk * BLOCK);
+          tc::tma_load_2d(sa + A_BYTES, &tmap_b, full_bar(stage), kb * BLOCK, n_blk * BN);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -97,7 +110,7 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::make_idesc(0, 0, BLOCK, BLOCK, 0, 0);
+      constexpr uint32_t idesc = tc::make_idesc(0, 0, BLOCK, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;  // running K-block counter across tiles -> TMEM buffer ring
@@ -110,7 +123,7 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tc::tc_fence_after();
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_BYTES;
-          const uint32_t tmem_d = tmem_base + buf * BLOCK;
+          const uint32_t tmem_d = tmem_base + buf * BN;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const uint64_t adesc = tc::make_smem_desc_sw128(sa + k * 32, 1024, 16);
@@ -127,19 +140,24 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else {
-    const int quarter = warp & 3;
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;      // which half of the tile's columns
     OutT* out = static_cast<OutT*>(p.out);
     const OutT* bias = static_cast<const OutT*>(p.bias);
+    const int nsb = ceil_div(p.N, BLOCK);  // weight scale blocks along N
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
       const int row = m_blk * BLOCK + quarter * 32 + lane;
       const bool row_ok = row < p.M;
+      const int col_base = n_blk * BN + half * COLS;
+      const int sblk = col_base / BLOCK;
+      const bool blk_ok = sblk < nsb;      // the tile's second half may lie past N
       const float* as_row = p.as + static_cast<int64_t>(row_ok ? row : 0) * p.as_row;
-      const float* bs_row = p.bs + static_cast<int64_t>(n_blk) * p.bs_row;
-      float2 acc[64];
+      const float* bs_row = p.bs + static_cast<int64_t>(blk_ok ? sblk : 0) * p.bs_row;
+      float2 acc[COLS / 2];
 #pragma unroll
-      for (int j = 0; j < 64; ++j) acc[j] = make_float2(0.f, 0.f);
+      for (int j = 0; j < COLS / 2; ++j) acc[j] = make_float2(0.f, 0.f);
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int buf = it % NBUF;
         const uint32_t buf_phase = (it / NBUF) & 1u;
@@ -147,28 +165,31 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const float2 s2 = make_float2(s, s);
         tc::mbar_wait(tfull_bar(buf), buf_phase);
         tc::tc_fence_after();
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + buf * BLOCK;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + buf * BN +
+                               half * COLS;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < COLS / 32; ++c) {
           uint32_t r[32];
           tc::tmem_ld32(taddr + c * 32, r);
           tc::tmem_ld_wait();
+          if (c == COLS / 32 - 1) {  // the whole partial is in registers: hand the buffer back before the math
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(tempty_bar(buf));
+          }
 #pragma unroll
           for (int j = 0; j < 16; ++j)
             acc[c * 16 + j] = ffma2(
                 make_float2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1])), s2,
                 acc[c * 16 + j]);
         }
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(tempty_bar(buf));
       }
-      if (row_ok) {
+      if (row_ok && blk_ok) {
         OutT* orow = out + static_cast<int64_t>(row) * p.ldc;
-        const int col0 = n_blk * BLOCK;
-        if (col0 + BLOCK <= p.N && (p.ldc & 7) == 0) {
+        const int col0 = col_base;
+        if (col0 + COLS <= p.N && (p.ldc & 7) == 0) {
 #pragma unroll
-          for (int v = 0; v < 16; ++v) {
+          for (int v = 0; v < COLS / 8; ++v) {
             uint32_t packed[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -184,7 +205,7 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < 64; ++j) {
+          for (int j = 0; j < COLS / 2; ++j) {
             const int c = col0 + 2 * j;
             if (c < p.N) orow[c] = from_float<OutT>(acc[j].x + (bias ? to_float<OutT>(bias[c]) : 0.f));
             if (c + 1 < p.N)
@@ -197,32 +218,41 @@ fp8_block_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, NBUF * BLOCK);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, NBUF * BN);
 }
 
-template <typename OutT>
-static int launch_block_gemm(const void* a, int64_t lda, const void* b, int64_t ldb,
-                             const BlockGemmParams& p, cudaStream_t st) {
-  constexpr int SMEM = kBlkStages * 2 * 128 * 128 + (2 * kBlkStages + 2 * kBlkBufs) * 8 + 16 + 1024;
+template <typename OutT, int BN>
+static int launch_block_gemm_bn(const void* a, int64_t lda, const void* b, int64_t ldb,
+                                const BlockGemmParams& p, cudaStream_t st) {
+  constexpr int SMEM = BlkCfg<BN>::SMEM;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d(&ta, a, p.M, p.K, lda, 128, 128, 1, false);
   if (rc) return rc;
-  rc = make_tmap_2d(&tb, b, p.N, p.K, ldb, 128, 128, 1, true);
+  rc = make_tmap_2d(&tb, b, p.N, p.K, ldb, BN, 128, 1, true);
   if (rc) return rc;
-  auto kern = fp8_block_gemm_kernel<OutT>;
+  auto kern = fp8_block_gemm_kernel<OutT, BN>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_done = true;
   }
-  const int tiles = ceil_div(p.M, 128) * ceil_div(p.N, 128);
+  const int tiles = ceil_div(p.M, 128) * ceil_div(p.N, BN);
   const int sms = device_sm_count();
   {
     ScopedKernelTimer timer("fp8_block_gemm", st);
-    B200_CUDA_OK(launch_kernel(kern, dim3(tiles < sms ? tiles : sms), dim3(192), SMEM, st, 1, pdl_family(p.M, kPdlGemmBig), ta, tb, p));
+    B200_CUDA_OK(launch_kernel(kern, dim3(tiles < sms ? tiles : sms), dim3(kBlkThreads), SMEM, st, 1, pdl_family(p.M, kPdlGemmBig), ta, tb, p));
   }
   B200_CHECK_LAUNCH("fp8_block_gemm_kernel");
   return 0;
+}
+
+template <typename OutT>
+static int launch_block_gemm(const void* a, int64_t lda, const void* b, int64_t ldb,
+                             const BlockGemmParams& p, cudaStream_t st) {
+  // 128 x 256 tiles once they give every SM at least ~1.5 tiles, else 128 x 128
+  const int tiles256 = ceil_div(p.M, 128) * ceil_div(p.N, 256);
+  if (2 * tiles256 >= 3 * device_sm_count()) return launch_block_gemm_bn<OutT, 256>(a, lda, b, ldb, p, st);
+  return launch_block_gemm_bn<OutT, 128>(a, lda, b, ldb, p, st);
 }
 
 }  // namespace b200

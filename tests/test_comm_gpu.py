@@ -204,7 +204,8 @@ def _mp_worker(rank, world, port, out_dir):
         assert torch.equal(out.cpu(), OA.all_reduce_oracle(xs)), numel
         nccl = mine.clone()
         dist.all_reduce(nccl)
-        torch.testing.assert_close(out.float(), nccl.float(), rtol=2e-2, atol=2e-2)
+        # NCCL rounds to bf16 between its reduction steps: allow one bf16 ulp of the largest sums
+        torch.testing.assert_close(out.float(), nccl.float(), rtol=2e-2, atol=2e-2 * world)
     # message above max_size falls back to NCCL
     big = torch.ones(comm.max_size // 2 + 64, dtype=torch.bfloat16, device="cuda")
     assert comm.custom_all_reduce(big) is None
