@@ -152,23 +152,27 @@ int splitk_pick(int tiles, int num_kb, int sms) {
 
 // Row-parallel fusion: the small-M kernel can reduce across the TP group in its epilogue when the
 // dense [M, N] partial fits one receive slot and the grid fits the flag table.
-// Policy measured at TP = 2 on B200 (profiles/r01_bench_allreduce_tp2.json): fusing wins while the
+// Policy measured on B200: at TP = 2 (profiles/r01_bench_allreduce_tp2.json) fusing wins while the
 // swap-AB kernel itself is the right GEMM (M <= 32: 7.7 vs 8.2 us at M = 1, 13.1 vs 15.4 us at
-// M = 32, against GEMM + stand-alone LL all-reduce); above that the big-tile GEMM + all-reduce is
-// faster.  b200_comm_fuse_config / B200_COMM_FUSE_MAX_M override.
+// M = 32, against GEMM + stand-alone LL all-reduce).  At TP = 8 (profiles/r01_bench_allreduce_tp8.json)
+// every tile pushes to 7 peers and the fused epilogue only wins at the smallest batches (o_proj:
+// 8.4 vs 10.8 us at M = 1 but 16.1 vs 12.7 at M = 8 and 51.6 vs 20.2 at M = 32), so the limit
+// shrinks with the group: 32 / 8 / 4 tokens at world 2 / 4 / 8 (world 4 interpolated).
+// b200_comm_fuse_config / B200_COMM_FUSE_MAX_M override.
 static std::atomic<int> g_fuse_max_m{-1};
-static int fuse_max_m() {
+static int fuse_max_m(int world) {
   int v = g_fuse_max_m.load(std::memory_order_relaxed);
   if (v < 0) {
-    v = env_int("B200_COMM_FUSE_MAX_M", 32);
-    g_fuse_max_m.store(v, std::memory_order_relaxed);
+    static const int env = env_int("B200_COMM_FUSE_MAX_M", -1);
+    v = env >= 0 ? env : (world <= 2 ? 32 : world <= 4 ? 8 : 4);
   }
   return v > 128 ? 128 : v;
 }
 
 bool comm_can_fuse(const void* comm, int M, int N) {
-  if (!comm || M > fuse_max_m()) return false;
+  if (!comm) return false;
   const Comm* c = static_cast<const Comm*>(comm);
+  if (M > fuse_max_m(c->dev.world)) return false;
   // LL words: one 8-byte word per (token pair, channel), pairs padded per cluster rank (S <= 8)
   return static_cast<uint64_t>(M / 2 + 8) * N * 8 <= c->dev.slot_bytes &&
          ceil_div(N, 128) * 8 <= kCommMaxBlocks;

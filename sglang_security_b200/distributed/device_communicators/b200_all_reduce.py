@@ -58,6 +58,10 @@ class B200AllReduce:
                                         ctypes.byref(h)), "b200_comm_create")
         self.handle = h
         self.max_size = int(lib.b200_comm_max_bytes(h))
+        # measured crossover with NCCL (NVLS) on 8 x B200 (profiles/r01_bench_allreduce_tp8.json): the
+        # one-shot kernel is 24 vs 36 us at 1 MiB, equal at 2 MiB, 70 vs 61 us at 4 MiB; at TP = 2 it
+        # stays ahead up to the 4 MiB buffer limit
+        self.crossover = self.max_size if self.world_size <= 4 else min(self.max_size, 2 << 20)
         self.disabled = False
         dist.barrier(group=group)  # every rank has zeroed + mapped all buffers before first use
 
@@ -104,7 +108,7 @@ class B200AllReduce:
             return False
         if not is_weak_contiguous(inp):
             return False
-        return inp_size <= self.max_size
+        return inp_size <= self.crossover
 
     # -- collectives ---------------------------------------------------------------------------
     def all_reduce(self, inp: torch.Tensor, *, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -175,7 +175,12 @@ class RowParallelLinear(LinearBase):
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
         if self.reduce_results and self.tp_size > 1:
             comm = get_tp_custom_all_reduce()
-            if comm is not None and getattr(self.quant_method, "supports_fused_all_reduce", False):
+            # the peer-memory path (fused epilogue or stand-alone one-shot kernel, chosen inside the
+            # library) only up to the measured crossover with NCCL for this group size
+            tokens = input_.numel() // max(1, input_.shape[-1])
+            out_bytes = tokens * self.output_size * input_.element_size()
+            if (comm is not None and out_bytes <= getattr(comm, "crossover", 0)
+                    and getattr(self.quant_method, "supports_fused_all_reduce", False)):
                 # GEMM -> all-reduce as one call: the decode-regime kernel reduces in its epilogue
                 self.fused_all_reduce = comm
                 try:
