@@ -11,8 +11,9 @@
 // (page_size 1) with 16-byte cp.async into 128-byte-swizzled shared memory — exactly the layout a
 // SWIZZLE_128B TMA box would produce, so tcgen05.mma consumes it through ordinary UMMA descriptors.
 //
-//   warps 0-3 : softmax.  Thread = one query row.  S tile (128 x 64 fp32) is read from TMEM twice
-//               (row max, then exp2 + bf16 P written to swizzled smem).  O stays in TMEM and is only
+//   warps 0-3 : softmax.  Thread = one query row.  The S tile (128 x 64 fp32) is read from TMEM once
+//               into registers and the accumulator released immediately (QK of the next tile runs
+//               under this tile's max / exp2 / pack); bf16 P goes to swizzled smem.  O stays in TMEM and is only
 //               rescaled when a row max grows by more than 2^8 (lazy rescale), so the common tile
 //               costs no TMEM round trip.
 //   warp 4    : MMA issuer (one thread): S = Q K^T (M128 N64 K16 x D/16), O += P V
@@ -151,22 +152,38 @@ attn_extend_kernel(const ExtendParams p) {
     cp_async_commit();
     // Tile j is issued only after tile j-1 has landed and been published: the MMA warp waits for
     // tile j+1 before it issues PV(j), so publishing must never sit behind a kv_empty wait.
+    // A thread owns one 16-byte column of rows lrow + RPP*i; the slot ids of tile j+1 are fetched
+    // while tile j is in flight, so the gather itself never waits on a req_to_token load.
+    constexpr int RPP = kLoaders / CPR;                 // rows per pass (6 for D = 128)
+    constexpr int PASSES = (kKvTile + RPP - 1) / RPP;
+    const int lrow = lt / CPR, lcol = lt - lrow * CPR;
+    int32_t slots[PASSES];
+    auto load_slots = [&](int j) {
+#pragma unroll
+      for (int i = 0; i < PASSES; ++i) {
+        const int pos = j * kKvTile + lrow + RPP * i;
+        slots[i] = (lrow + RPP * i < kKvTile && pos < kv_len) ? __ldg(rtt + pos) : 0;  // 0 = dummy row
+      }
+    };
     auto issue_tile = [&](int j) {
       const int stage = j & 1;
       const uint32_t sk = sbase + C::OFF_K + stage * C::KV_TILE_BYTES;
       const uint32_t sv = sbase + C::OFF_V + stage * C::KV_TILE_BYTES;
-      for (int c = lt; c < kKvTile * CPR; c += kLoaders) {
-        const int r = c / CPR, col = c - r * CPR;
-        const int pos = j * kKvTile + r;
-        const int64_t slot = pos < kv_len ? __ldg(rtt + pos) : 0;  // 0 = dummy row (masked later)
-        const int64_t off = slot * row_bytes + col * 16;
-        const uint32_t so = swz_off<kKvTile>(r, col);
-        cp_async16(sk + so, kbase + off);
-        cp_async16(sv + so, vbase + off);
+#pragma unroll
+      for (int i = 0; i < PASSES; ++i) {
+        const int r = lrow + RPP * i;
+        if (r < kKvTile) {
+          const int64_t off = static_cast<int64_t>(slots[i]) * row_bytes + lcol * 16;
+          const uint32_t so = swz_off<kKvTile>(r, lcol);
+          cp_async16(sk + so, kbase + off);
+          cp_async16(sv + so, vbase + off);
+        }
       }
       cp_async_commit();
     };
+    load_slots(0);
     issue_tile(0);
+    if (n_kv > 1) load_slots(1);
     cp_async_wait<1>();  // Q landed
     tc::fence_proxy_async_smem();
     tc::mbar_arrive(bar_q);
@@ -176,6 +193,7 @@ attn_extend_kernel(const ExtendParams p) {
       tc::mbar_arrive(bar_kv_full((j - 1) & 1));
       if (j >= 2) tc::mbar_wait(bar_kv_empty(j & 1), ((j >> 1) - 1) & 1u);  // PV(j-2) done
       issue_tile(j);
+      if (j + 1 < n_kv) load_slots(j + 1);
     }
     cp_async_wait<0>();
     tc::fence_proxy_async_smem();
@@ -245,16 +263,23 @@ attn_extend_kernel(const ExtendParams p) {
     for (int j = 0; j < n_kv; ++j) {
       tc::mbar_wait(bar_s_full, j & 1u);
       tc::tc_fence_after();
-      // ---- pass 1: row max of this tile
+      // ---- S(j) -> registers in ONE TMEM read; the accumulator is handed back at once so the MMA
+      //      warp issues QK(j+1) while this tile's max / exp2 / pack run from registers
+      uint32_t v[2][32];
+      tc::tmem_ld32(tmem_s, v[0]);
+      tc::tmem_ld32(tmem_s + 32, v[1]);
+      tc::tmem_ld_wait();
+      tc::tc_fence_before();
+      tc::mbar_arrive(bar_s_free);
       float mt = -INFINITY;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        uint32_t v[32];
-        tc::tmem_ld32(tmem_s + h * 32, v);
-        tc::tmem_ld_wait();
+      for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int c = 0; c < 32; ++c) mt = fmaxf(mt, score(v[c], j * kKvTile + h * 32 + c));
-      }
+        for (int c = 0; c < 32; ++c) {
+          const float sc = score(v[h][c], j * kKvTile + h * 32 + c);
+          v[h][c] = __float_as_uint(sc);
+          mt = fmaxf(mt, sc);
+        }
       const float m_new = fmaxf(m, mt);
       const bool need = m_new > m + kRescaleThreshold;  // also true for the first finite max
       bool pv_waited = false;
@@ -266,12 +291,12 @@ attn_extend_kernel(const ExtendParams p) {
           const float alpha = (m == -INFINITY) ? 0.f : fast_exp2(m - m_new);
 #pragma unroll 1
           for (int cc = 0; cc < D / 32; ++cc) {
-            uint32_t v[32];
-            tc::tmem_ld32(tmem_o + cc * 32, v);
+            uint32_t o[32];
+            tc::tmem_ld32(tmem_o + cc * 32, o);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int c = 0; c < 32; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) * alpha);
-            tc::tmem_st32(tmem_o + cc * 32, v);
+            for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+            tc::tmem_st32(tmem_o + cc * 32, o);
           }
           tc::tmem_st_wait();
           l *= alpha;
@@ -279,44 +304,37 @@ attn_extend_kernel(const ExtendParams p) {
         m = m_new;
       }
       const float m_use = (m == -INFINITY) ? 0.f : m;
+      // ---- P = exp2(S - m), 16-bit, packed in registers first
+      uint32_t packed[2][16];
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float p0 = fast_exp2(__uint_as_float(v[h][2 * c]) - m_use);
+          const float p1 = fast_exp2(__uint_as_float(v[h][2 * c + 1]) - m_use);
+          l += p0 + p1;
+          if (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(p0, p1);
+            packed[h][c] = *reinterpret_cast<uint32_t*>(&t2);
+          } else {
+            __half2 t2 = __floats2half2_rn(p0, p1);
+            packed[h][c] = *reinterpret_cast<uint32_t*>(&t2);
+          }
+        }
       if (j > 0 && !pv_waited) {
         tc::mbar_wait(bar_pv_full, (j - 1) & 1u);  // PV(j-1) has finished reading P(j-1)
         tc::tc_fence_after();
       }
-      // ---- pass 2: P = exp2(S - m), bf16, into swizzled smem (A operand of the PV MMA)
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        uint32_t v[32];
-        tc::tmem_ld32(tmem_s + h * 32, v);
-        tc::tmem_ld_wait();
-        if (h == 1) {
-          tc::tc_fence_before();
-          tc::mbar_arrive(bar_s_free);  // S(j) fully consumed by this thread
-        }
-        uint32_t packed[16];
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          const int kpos = j * kKvTile + h * 32 + 2 * c;
-          const float p0 = fast_exp2(score(v[2 * c], kpos) - m_use);
-          const float p1 = fast_exp2(score(v[2 * c + 1], kpos + 1) - m_use);
-          l += p0 + p1;
-          if (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
-            __nv_bfloat162 t2 = __floats2bfloat162_rn(p0, p1);
-            packed[c] = *reinterpret_cast<uint32_t*>(&t2);
-          } else {
-            __half2 t2 = __floats2half2_rn(p0, p1);
-            packed[c] = *reinterpret_cast<uint32_t*>(&t2);
-          }
-        }
+      for (int h = 0; h < 2; ++h)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int chunk = h * 4 + i;
           const uint32_t addr = sbase + C::OFF_P + r * 128 + ((chunk ^ (r & 7)) << 4);
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(packed[4 * i]),
-                       "r"(packed[4 * i + 1]), "r"(packed[4 * i + 2]), "r"(packed[4 * i + 3])
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(packed[h][4 * i]),
+                       "r"(packed[h][4 * i + 1]), "r"(packed[h][4 * i + 2]), "r"(packed[h][4 * i + 3])
                        : "memory");
         }
-      }
       tc::fence_proxy_async_smem();
       tc::tc_fence_before();
       tc::mbar_arrive(bar_p_full);
