@@ -191,7 +191,7 @@ struct W4Cfg {
   static constexpr int XSUB = BM * 128, BSUB = BK * BN * 2;
   static constexpr int X_BYTES = KS * XSUB, B_BYTES = KS * BSUB, STAGE_BYTES = X_BYTES + B_BYTES;
   static constexpr int RAW_BYTES = KS * (kW4PackedBytes + kW4ZsBytes);
-  static constexpr int ST = (!SWAP && BM == 256) ? 4 : 3;   // operand stages
+  static constexpr int ST = BM == 256 ? (SWAP ? 2 : 4) : 3;  // operand stages
   static constexpr int RAWS = SWAP ? (BM == 32 ? 10 : BM == 64 ? 8 : 3) : (BM == 256 ? 5 : 3);  // packed stages
   static constexpr int ACC_COLS = BM;  // fp32 columns per accumulator set
   static constexpr int TMEM_COLS = 2 * ACC_COLS < 32 ? 32 : 2 * ACC_COLS;
@@ -653,18 +653,22 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
 // Tile selection.  M <= 64: swap-AB (tokens are the UMMA N dimension).  Otherwise 128-row tiles, or
 // 256-row tiles (half the dequant work per flop) once they still fill the machine.
-// B200_W4_BM=32|64|129 (swap) |128|256 overrides (sweeps).
-static int w4_pick_bm(int M, int N, int sms) {
+// B200_W4_BM=32|64|129|257 (swap) |128|256 overrides (sweeps).
+static int w4_pick_bm(int M, int N, int K, int sms) {
   static int forced = [] {
     const char* v = std::getenv("B200_W4_BM");
     return v && *v ? std::atoi(v) : 0;
   }();
   if ((forced == 32 || forced == 64) && M <= forced) return forced;
   if (forced == 129 && M <= 128) return forced;
+  if (forced == 257 && M <= 256) return forced;
   if (forced == 128 || forced == 256) return forced;
   if (M <= 32) return 32;
   if (M <= 64) return 64;
   if (M <= 128) return ceil_div(N, 128) <= 64 ? 129 : 128;  // 129 = swap-AB with 128 tokens (split-K)
+  // 257 = swap-AB with 256 tokens (split-K): only two operand stages fit, which pays for deep K only
+  // (down_proj 5120 x 13824: 64.5 -> 50-52 us; 5120 x 2560: 17 -> 25-30 us, so not there)
+  if (M <= 256 && ceil_div(N, 128) <= 40 && K >= 8192) return 257;
   return ceil_div(M, 256) * ceil_div(N, 128) >= (sms * 3) / 4 ? 256 : 128;
 }
 
@@ -823,7 +827,7 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   p.raw_tma = 0;
   p.kb_per_split = 0;
-  const int bm = w4_pick_bm(M, N, device_sm_count());
+  const int bm = w4_pick_bm(M, N, K, device_sm_count());
   // dequant warp layout: 8 warps in DG groups that own alternate stages.  B200_W4_CFG: 0 = one
   // group, 1 = two groups (default)
   static const int cfg = [] {
@@ -834,6 +838,7 @@ int b200_w4a16_gemm(const void* x, int64_t ldx, const void* qweight, const void*
   (bm == 256  ? launch_w4a16_gemm<TT, 256, false, DQ_, DG_>(x, ldx, p, st)              \
    : bm == 128 ? launch_w4a16_gemm<TT, 128, false, DQ_, DG_>(x, ldx, p, st)             \
    : bm == 129 ? launch_w4a16_gemm<TT, 128, true, DQ_, DG_>(x, ldx, p, st)              \
+   : bm == 257 ? launch_w4a16_gemm<TT, 256, true, DQ_, DG_>(x, ldx, p, st)              \
    : bm == 64  ? launch_w4a16_gemm<TT, 64, true, DQ_, DG_>(x, ldx, p, st)               \
                : launch_w4a16_gemm<TT, 32, true, DQ_, DG_>(x, ldx, p, st))
 #define B200_W4_LAUNCH(TT) (cfg == 0 ? B200_W4_LAUNCH_C(TT, 8, 1) : B200_W4_LAUNCH_C(TT, 8, 2))

@@ -71,7 +71,7 @@ def _awq_layer(k, n, group, dtype, seed, realistic=False):
             _rand_i32((k // group, n // 8), seed + 1))
 
 
-@pytest.mark.parametrize("m", [1, 16, 24, 64, 100, 130, 1024])
+@pytest.mark.parametrize("m", [1, 16, 24, 64, 100, 130, 256, 1024])
 @pytest.mark.parametrize("k,n,group", [(512, 256, 128), (5120, 3584, 128), (2560, 5120, 128),
                                        (256, 136, 32), (1024, 1000, 64)])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
@@ -95,6 +95,22 @@ def test_awq_linear_method(m, k, n, group, dtype):
     out, _ = layer(x.cuda())
     ref = O.w4a16_linear_oracle(x, O.awq_dequantize_oracle(qweight, scales, qzeros, group), bias)
     # reference tolerance for x @ dequant in 16 bit: rtol 1e-2 (SURVEY §8d cfg 4)
+    err = (out.cpu().float() - ref.float()).abs()
+    tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
+    assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
+
+
+@pytest.mark.parametrize("m", [130, 256])
+def test_awq_deep_k_swap256(m):
+    """K >= 8192 with few column tiles takes the 256-token swap-AB / split-K instance."""
+    from sglang_security_b200.layers.quantization.w4a16_kernel import unpack_zeros, w4a16_gemm
+
+    k, n, group, dtype = 8192, 384, 128, torch.bfloat16
+    qweight, scales, qzeros = _awq_layer(k, n, group, dtype, seed=3, realistic=True)
+    x = torch.randn((m, k), generator=torch.Generator().manual_seed(5)).to(dtype)
+    z = unpack_zeros(qzeros.cuda(), dtype, True, False)
+    out = w4a16_gemm(x.cuda(), qweight.cuda(), z, scales.cuda(), group)
+    ref = O.w4a16_linear_oracle(x, O.awq_dequantize_oracle(qweight, scales, qzeros, group), None)
     err = (out.cpu().float() - ref.float()).abs()
     tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
     assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
