@@ -54,16 +54,24 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(threads) : "memory");
 }
 
-template <int MT, bool BLK>
+template <int MT, bool BLK, int KSUB = 1>
 struct SmallMCfg {
-  static constexpr int W_BYTES = 128 * 128;
-  static constexpr int X_BYTES = MT * 128;
+  // A ring slot ("block") spans KS sub-blocks of 128 K: every barrier hand-off of the pipeline costs
+  // a fixed ~0.3 us round trip per role (profiles/r01_w4a16_notes.md), so the decode instances
+  // can move 32 KiB of weights per hand-off (KSUB = 2): measured +5-8 % on the wide weights
+  // (gate_up M = 1: 20.7 -> 19.6 us = 6.0 TB/s, 92 % of the HBM peak; down 11.1 us) but -7 % on
+  // qkv / o, whose short K slices then hold too few blocks, so the launcher picks it by weight size.
+  // The block-scaled variant needs one TMEM buffer per 128 K and keeps KS = 1.
+  static constexpr int KS = (!BLK && MT <= 32) ? KSUB : 1;
+  static constexpr int W_SUB = 128 * 128, X_SUB = MT * 128;
+  static constexpr int W_BYTES = KS * W_SUB;
+  static constexpr int X_BYTES = KS * X_SUB;
   // Two CTAs per SM (one for the 128-token block-scaled variant whose accumulators need all
   // registers).  The weight ring is as deep as shared memory allows — the kernel is bound by bytes
   // in flight (measured: 3/4/5 stages -> 3.2/4.4/5.7 TB/s) — while the activation ring, fed from
   // L2 and identical for every CTA, is only NX deep and lags the weight ring.
   static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : 112 * 1024;
-  static constexpr int NX = MT <= 32 ? 3 : 2;
+  static constexpr int NX = (MT <= 32 && KS == 1) ? 3 : 2;
   static constexpr int NW = (BUDGET - NX * X_BYTES) / W_BYTES;
   static constexpr int NBUF = BLK ? (MT <= 64 ? 4 : 2) : 1;
   static constexpr int TCOLS = (NBUF * MT) < 32 ? 32 : NBUF * MT;
@@ -77,11 +85,11 @@ struct SmallMCfg {
 
 // AR: the epilogue reduces across the tensor-parallel group (p.comm); a separate instantiation so
 // the plain kernel's unrolled epilogue carries none of that code (it cost 12-26 % at M = 16-32).
-template <int MT, bool BLK, typename OutT, bool AR>
+template <int MT, bool BLK, typename OutT, bool AR, int KSUB>
 __global__ void __launch_bounds__(192, (BLK && MT == 128) ? 1 : 2)
 fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
                        const __grid_constant__ CUtensorMap tmap_x, const SmallMParams p) {
-  using C = SmallMCfg<MT, BLK>;
+  using C = SmallMCfg<MT, BLK, KSUB>;
   constexpr int NW = C::NW, NX = C::NX, NBUF = C::NBUF;
   extern __shared__ __align__(1024) uint8_t smem_raw[];  // SWIZZLE_128B tiles need 1024-byte alignment
   const uint32_t smem_base = smem_u32(smem_raw);
@@ -101,7 +109,7 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
   const uint32_t rank = cluster_ctarank();
   const uint32_t S = cluster_nctarank();
   const int n_tile = blockIdx.x / S;
-  const int num_kb = ceil_div(p.K, 128);
+  const int num_kb = ceil_div(p.K, 128 * C::KS);
   const int kb0 = min(num_kb, static_cast<int>(rank) * p.kb_per_split);
   const int kb1 = min(num_kb, kb0 + p.kb_per_split);
   const int nkb = kb1 - kb0;
@@ -113,11 +121,16 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
     const int s = i % NW;
     tc::mbar_arrive_expect_tx(full_bar(s), C::W_BYTES + C::X_BYTES);
     const uint32_t sw = smem_base + s * C::W_BYTES;
-    tc::tma_load_2d_hint(sw, &tmap_w, full_bar(s), (kb0 + i) * 128, n_tile * 128, tc::kEvictFirst);
+#pragma unroll
+    for (int u = 0; u < C::KS; ++u)
+      tc::tma_load_2d_hint(sw + u * C::W_SUB, &tmap_w, full_bar(s), ((kb0 + i) * C::KS + u) * 128,
+                           n_tile * 128, tc::kEvictFirst);
   };
   auto issue_x = [&](int i) {
-    tc::tma_load_2d_hint(ring_x + (i % NX) * C::X_BYTES, &tmap_x, full_bar(i % NW),
-                         (kb0 + i) * 128, 0, tc::kEvictLast);
+#pragma unroll
+    for (int u = 0; u < C::KS; ++u)
+      tc::tma_load_2d_hint(ring_x + (i % NX) * C::X_BYTES + u * C::X_SUB, &tmap_x, full_bar(i % NW),
+                           ((kb0 + i) * C::KS + u) * 128, 0, tc::kEvictLast);
   };
   auto wait_mma_done = [&](int i) { tc::mbar_wait(empty_bar(i % NW), (i / NW) & 1u); };
 
@@ -179,11 +192,14 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
         const uint32_t sx = ring_x + (i % NX) * C::X_BYTES;
         const uint32_t tmem_d = tmem_base + buf * MT;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t adesc = tc::make_smem_desc_sw128(sw + k * 32, 1024, 16);
-          const uint64_t bdesc = tc::make_smem_desc_sw128(sx + k * 32, 1024, 16);
-          const uint32_t accum = BLK ? (k != 0) : ((i != 0) | (k != 0));
-          tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, accum ? 1u : 0u);
+        for (int u = 0; u < C::KS; ++u) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adesc = tc::make_smem_desc_sw128(sw + u * C::W_SUB + k * 32, 1024, 16);
+            const uint64_t bdesc = tc::make_smem_desc_sw128(sx + u * C::X_SUB + k * 32, 1024, 16);
+            const uint32_t accum = BLK ? (k != 0) : ((i != 0) | (u != 0) | (k != 0));
+            tc::mma_f8f6f4(tmem_d, adesc, bdesc, idesc, accum ? 1u : 0u);
+          }
         }
         tc::mma_commit(empty_bar(i % NW));
         if (BLK) tc::mma_commit(tfull_bar(buf));
@@ -373,16 +389,16 @@ bool smallm_forced();                      // threshold set explicitly through t
 bool comm_can_fuse(const void* comm, int M, int N);
 int comm_all_reduce_rows(void* comm, void* out, int64_t ldc, int M, int N, int dtype, void* stream);
 
-template <int MT, bool BLK, typename OutT, bool AR>
-int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallMParams p,
-                  cudaStream_t st, const char* timer_name) {
-  using C = SmallMCfg<MT, BLK>;
+template <int MT, bool BLK, typename OutT, bool AR, int KSUB>
+int launch_smallm_ks(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallMParams p,
+                     cudaStream_t st, const char* timer_name) {
+  using C = SmallMCfg<MT, BLK, KSUB>;
   CUtensorMap tw, tx;
   int rc = make_tmap_2d(&tw, w, p.N, p.K, ldw, 128, 128, 1, true);
   if (rc) return rc;
   rc = make_tmap_2d(&tx, x, p.M, p.K, ldx, MT, 128, 1, false);
   if (rc) return rc;
-  auto kern = fp8_gemm_smallm_kernel<MT, BLK, OutT, AR>;
+  auto kern = fp8_gemm_smallm_kernel<MT, BLK, OutT, AR, KSUB>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -390,8 +406,10 @@ int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallM
     attr_done = true;
   }
   const int n_tiles = ceil_div(p.N, 128);
-  const int num_kb = ceil_div(p.K, 128);
-  const int S = smallm_pick_splits(n_tiles, num_kb);
+  // the split factor is chosen on 128-wide K blocks as before; slices are whole ring blocks
+  int S = smallm_pick_splits(n_tiles, ceil_div(p.K, 128));
+  const int num_kb = ceil_div(p.K, 128 * C::KS);
+  if (S > num_kb) S = num_kb;
   p.kb_per_split = ceil_div(num_kb, S);
   p.pdl_late = pdl_late();
   {
@@ -400,6 +418,17 @@ int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, SmallM
   }
   B200_CHECK_LAUNCH("fp8_gemm_smallm_kernel");
   return 0;
+}
+
+template <int MT, bool BLK, typename OutT, bool AR>
+int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, const SmallMParams& p,
+                  cudaStream_t st, const char* timer_name) {
+  if constexpr (!BLK && MT <= 32 && !AR) {
+    // 256-K ring blocks for weights of 48 MB and more (gate_up, down_proj of the named models)
+    if (static_cast<int64_t>(p.N) * p.K >= (48ll << 20))
+      return launch_smallm_ks<MT, BLK, OutT, AR, 2>(x, ldx, w, ldw, p, st, timer_name);
+  }
+  return launch_smallm_ks<MT, BLK, OutT, AR, 1>(x, ldx, w, ldw, p, st, timer_name);
 }
 
 template <bool BLK>
