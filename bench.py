@@ -16,7 +16,8 @@ has no collective, total work is fixed => "strong" scaling.
   e2e     : tokens/s through the plugin API with the step's inputs (fused qkv activations of all
             layers + ForwardBatch index tensors) copied from pinned host memory and the outputs
             copied back to pinned host memory inside the timed region (the KV pool is the path's
-            resident state, like weights, and is not a per-step input)
+            resident state, like weights, and is not a per-step input); the copies run on
+            side streams layer by layer, overlapped with the attention of the neighbouring layers
   roofline: dominant kernel attn_decode_split, algorithmic bytes per launch / CUDA-event time
   cpu_baseline / --impl reference: the reference's own CPU decode kernel
             (sgl-kernel/csrc/cpu/decode.cpp, prebuilt in oracle/_ref) on the host cores, on a
@@ -383,13 +384,34 @@ def run_b200(args):
     h2d_bytes = h_qkv.numel() * 2 + (h_req.numel() + h_lens.numel() + h_loc.numel()) * 8
     d2h_bytes = h_out.numel() * 2
 
+    # The copies run on their own streams, layer by layer: layer l+1's activations come in and
+    # layer l-1's output goes out while layer l computes.  Every copy of the step still happens
+    # inside the timed region, and the step only counts as done once its last output is on the host.
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    ev_in = [torch.cuda.Event() for _ in range(layers)]
+    ev_done = [torch.cuda.Event() for _ in range(layers)]
+
     def e2e_step():
-        d_qkv.copy_(h_qkv, non_blocking=True)
-        d_req.copy_(h_req, non_blocking=True)
-        d_lens.copy_(h_lens, non_blocking=True)
-        d_loc.copy_(h_loc, non_blocking=True)
-        step(True)
-        h_out.copy_(d_out, non_blocking=True)
+        cur = torch.cuda.current_stream()
+        s_in.wait_stream(cur)          # the previous step has consumed the device inputs
+        with torch.cuda.stream(s_in):
+            d_req.copy_(h_req, non_blocking=True)
+            d_lens.copy_(h_lens, non_blocking=True)
+            d_loc.copy_(h_loc, non_blocking=True)
+            for l in range(layers):
+                d_qkv[l].copy_(h_qkv[l], non_blocking=True)
+                ev_in[l].record(s_in)
+        cur.wait_event(ev_in[0])
+        backend.init_forward_metadata(fb)
+        for l in range(layers):
+            cur.wait_event(ev_in[l])
+            q, k, v = d_qkv[l].split([hq * d, hkv * d, hkv * d], dim=-1)
+            d_out[l].copy_(attn[l](q, k, v, fb))
+            ev_done[l].record(cur)
+            s_out.wait_event(ev_done[l])
+            with torch.cuda.stream(s_out):
+                h_out[l].copy_(d_out[l], non_blocking=True)
+        cur.wait_stream(s_out)         # the step's result is in host memory
 
     for _ in range(min(3, args.warmup)):
         e2e_step()
