@@ -702,8 +702,9 @@ static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStr
   }
   const int tiles = ceil_div(p.M, BM) * ceil_div(p.N, 128);
   const int sms = device_sm_count();
-  // split-K for the swap-AB kernels when the tiles alone leave most SMs idle: the largest power of
-  // two S <= 8 with tiles * S <= SMs and at least two stages per rank.  B200_W4_SPLITS forces it.
+  // split-K for the swap-AB kernels when the tiles alone leave most SMs idle: the largest S <= 8
+  // whose `tiles` clusters are co-resident in one wave with at least four stages per rank.
+  // B200_W4_SPLITS forces it.
   int S = 1;
   if (SWAP) {
     static const int forced = [] {
@@ -714,12 +715,36 @@ static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStr
     if (forced > 0) {
       S = forced;
     } else {
-      // clusters are placed inside one GPC (16-20 SMs): S CTAs x tiles must fit 8 GPCs in one wave
-      for (int c = 8; c >= 2; --c)
-        if (tiles <= 8 * (16 / c) && num_kb >= 4 * c) {
+      // clusters are placed inside one GPC and the SMs per GPC differ between boards (the same
+      // 40-tile x 3 launch ran in one wave on one B200 and two on another: 27.5 vs 39.7 us), so
+      // the driver is asked how many clusters of each size are co-resident; answers are cached
+      static int max_clusters[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      for (int c = 8; c >= 2; --c) {
+        if (num_kb < 4 * c || tiles > sms / c) continue;
+        if (max_clusters[c] == 0) {
+          cudaLaunchConfig_t cfg = {};
+          cfg.gridDim = dim3(c * 8);
+          cfg.blockDim = dim3((7 + DQ) * 32);
+          cfg.dynamicSmemBytes = C::SMEM;
+          cudaLaunchAttribute attr[1];
+          attr[0].id = cudaLaunchAttributeClusterDimension;
+          attr[0].val.clusterDim.x = c;
+          attr[0].val.clusterDim.y = 1;
+          attr[0].val.clusterDim.z = 1;
+          cfg.attrs = attr;
+          cfg.numAttrs = 1;
+          int n = 0;
+          if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+            (void)cudaGetLastError();
+            n = -1;
+          }
+          max_clusters[c] = n;
+        }
+        if (max_clusters[c] >= tiles) {
           S = c;
           break;
         }
+      }
     }
     while (S > 1 && (S - 1) * ceil_div(num_kb, S) >= num_kb) --S;
     p.kb_per_split = ceil_div(num_kb, S);
