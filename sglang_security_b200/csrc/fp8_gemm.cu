@@ -236,7 +236,11 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
   // kernel wins up to M = 32; from M = 33 the 128x128 tile split over K is faster on every
   // Llama-3.1-8B shape (10.8 vs 15.4-20.6 us at N = K = 4096, 17.2 vs 21.7-27 us at K = 14336).
   const bool fuse_ar = comm_can_fuse(comm, M, N);
-  if (fuse_ar || (M <= smallm_max_m() && (M <= 32 || smallm_forced()))) {
+  // Exception (profiles/r01_bench_gemm_midm_swap.json): a weight with more 128-row tiles than SMs
+  // (gate_up 28672x4096) cannot be split and runs the big tiles in two uneven waves; there the
+  // swap-AB kernel stays ahead up to M = 64 (27.4 vs 31.5 us at M = 48, 29.1 vs 31.7 at M = 64).
+  const bool wide = ceil_div(N, 128) > device_sm_count();
+  if (fuse_ar || (M <= smallm_max_m() && (M <= 32 || (wide && M <= 64) || smallm_forced()))) {
     SmallMParams sp = {};
     if (fuse_ar) {
       sp.use_comm = 1;
@@ -257,8 +261,15 @@ static int fp8_gemm_rowcol_impl(const void* a, int64_t lda, const void* b, int64
     return comm_all_reduce_rows(comm, out, ldc, M, N, out_dtype, stream);
   }
   // Tile choice: 128x256 when there is enough work to fill the SMs with it, else 128x128.
+  const int sms = device_sm_count();
   const int64_t tiles256 = static_cast<int64_t>(ceil_div(M, 128)) * ceil_div(N, 256);
-  const bool big = tiles256 >= device_sm_count();
+  bool big = tiles256 >= sms;
+  // Measured (profiles/r01_bench_gemm_tilewidth.json): in the weight-streaming regime below that
+  // the 256-wide tile does not pay even when it saves a wave (28672x4096, M <= 128: 34 vs 31.6 us;
+  // M = 192-256: 44-46 vs 46-47 us), so the rule stays.  B200_GEMM_BN = 128 / 256 forces the choice.
+  static const int force_bn = env_int("B200_GEMM_BN", 0);
+  if (force_bn == 128) big = false;
+  if (force_bn == 256) big = true;
   int rc;
   // pairs of M blocks share the weight tile by TMA multicast (B200_GEMM_MCAST=0 turns it off)
   static const int mcast_on = env_int("B200_GEMM_MCAST", 1);

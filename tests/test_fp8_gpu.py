@@ -236,6 +236,24 @@ def test_fp8_smallm_cluster_splitk_matches_oracle_and_big_tile_path(m, n, k, spl
     assert (out.float() - out_big.float()).abs().max().item() <= 2 ** -7 * scale
 
 
+@pytest.mark.parametrize("m", [33, 48, 64, 65])
+def test_fp8_scaled_mm_wide_weight_default_dispatch(m):
+    """A weight with more 128-row tiles than SMs (here 150) takes the swap-AB kernel up to M = 64 and
+    the big tiles above; both sides of the switch against the oracle with the library defaults."""
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_scaled_mm
+
+    n, k = 150 * 128, 384
+    g = torch.Generator().manual_seed(m + n)
+    a, b = _rand_fp8((m, k), g), _rand_fp8((n, k), g)
+    sa = torch.randn((m,), generator=g) * 0.001
+    sb = torch.randn((n,), generator=g) * 0.001
+    ref = O.scaled_mm_oracle(a, b.t(), sa, sb, torch.bfloat16, None)
+    out = fp8_scaled_mm(a.cuda(), b.cuda().t(), sa.cuda(), sb.cuda(), torch.bfloat16, None)
+    torch.testing.assert_close(out.cpu(), ref, rtol=0.02, atol=1)
+    scale = max(1.0, ref.float().abs().max().item())
+    assert (out.cpu().float() - ref.float()).abs().max().item() <= 2e-2 * scale
+
+
 @pytest.mark.parametrize("m", [1, 16, 31, 64, 83, 128])
 @pytest.mark.parametrize("n,k,splits", [(512, 7168, 0), (7168, 1024, 0), (1536, 2048, 8),
                                         (2112, 1152, 4), (128, 128, 1)])
