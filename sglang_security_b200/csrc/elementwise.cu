@@ -98,14 +98,48 @@ struct RowOut {
 // Writes one row held in registers as y[it][8] (values already rounded to T) to the 16-bit output
 // and/or quantises it.  The arithmetic of the quantisers is that of fp8_quant.cu, so fused and
 // unfused paths emit identical bytes.
+// A row may be split over the CTAs of a cluster (small token counts): this CTA then holds the
+// vectors i0 + threadIdx.x + it * kRowThreads < nvec (nvec = end of its window, i0 a multiple of 16 so
+// that 128-groups stay inside one CTA) and the per-token amax is combined across the cluster through
+// distributed shared memory — a maximum, so the result does not depend on the split.
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_size() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ float cluster_max(float v, float* slots /* [8] shared */) {
+  const uint32_t S = cluster_size();
+  if (S == 1) return v;
+  const uint32_t rank = cluster_rank();
+  if (threadIdx.x < S) {  // thread j publishes this CTA's value into CTA j's slot [rank]
+    uint32_t local = static_cast<uint32_t>(__cvta_generic_to_shared(slots + rank)), remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+    asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(remote), "f"(v) : "memory");
+  }
+  cluster_barrier();
+  float r = slots[0];
+  for (uint32_t j = 1; j < S; ++j) r = fmaxf(r, slots[j]);
+  return r;
+}
+
 template <typename T>
 __device__ __forceinline__ void emit_row(const float (&y)[kMaxIters][8], int nvec, int m,
-                                         const RowOut& o, float* red) {
+                                         const RowOut& o, float* red, int i0 = 0,
+                                         float* cl_slots = nullptr) {
   if (o.out) {
     T* orow = static_cast<T*>(o.out) + m * o.ldo;
 #pragma unroll
     for (int it = 0; it < kMaxIters; ++it) {
-      const int i = threadIdx.x + it * kRowThreads;
+      const int i = i0 + threadIdx.x + it * kRowThreads;
       if (i < nvec) st8(orow + i * 8, y[it]);
     }
   }
@@ -113,20 +147,21 @@ __device__ __forceinline__ void emit_row(const float (&y)[kMaxIters][8], int nve
     float amax = 0.f;
 #pragma unroll
     for (int it = 0; it < kMaxIters; ++it) {
-      const int i = threadIdx.x + it * kRowThreads;
+      const int i = i0 + threadIdx.x + it * kRowThreads;
       if (i < nvec) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(y[it][e]));
       }
     }
     amax = block_reduce<true>(amax, red);
+    if (cl_slots) amax = cluster_max(amax, cl_slots);
     const float scale = amax / kFp8MaxE;
-    if (threadIdx.x == 0) o.scales[m * o.s_row] = scale;
+    if (threadIdx.x == 0 && (!cl_slots || cluster_rank() == 0)) o.scales[m * o.s_row] = scale;
     const float inv = scale > 0.f ? 1.0f / scale : 0.f;
     uint8_t* qrow = o.q + m * o.ldq;
 #pragma unroll
     for (int it = 0; it < kMaxIters; ++it) {
-      const int i = threadIdx.x + it * kRowThreads;
+      const int i = i0 + threadIdx.x + it * kRowThreads;
       if (i < nvec) {
         uint32_t lo = 0, hi = 0;
 #pragma unroll
@@ -143,7 +178,7 @@ __device__ __forceinline__ void emit_row(const float (&y)[kMaxIters][8], int nve
     uint8_t* qrow = o.q + m * o.ldq;
 #pragma unroll
     for (int it = 0; it < kMaxIters; ++it) {
-      const int i = threadIdx.x + it * kRowThreads;  // 16 consecutive threads = one 128-group
+      const int i = i0 + threadIdx.x + it * kRowThreads;  // 16 consecutive threads = one 128-group
       float amax = o.eps;
       if (i < nvec) {
 #pragma unroll
@@ -177,10 +212,18 @@ __global__ void __launch_bounds__(kRowThreads)
 rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, int64_t ldr,
                const T* __restrict__ weight, int K, float eps, RowOut o) {
   __shared__ float red[32];
-  griddep_wait();
-  griddep_launch_dependents();
   const int m = blockIdx.x;
   const int nvec = K / 8;
+  // the norm weight does not depend on the previous kernel: fetch it before the dependency wait so
+  // its latency overlaps the predecessor's tail instead of following the reduction
+  uint4 wraw[kMaxIters];
+#pragma unroll
+  for (int it = 0; it < kMaxIters; ++it) {
+    const int i = threadIdx.x + it * kRowThreads;
+    wraw[it] = i < nvec ? __ldg(reinterpret_cast<const uint4*>(weight + i * 8)) : make_uint4(0, 0, 0, 0);
+  }
+  griddep_wait();
+  griddep_launch_dependents();
   const T* xrow = x + m * ldx;
   T* rrow = residual ? residual + m * ldr : nullptr;
   float y[kMaxIters][8];
@@ -207,10 +250,13 @@ rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, i
   for (int it = 0; it < kMaxIters; ++it) {
     const int i = threadIdx.x + it * kRowThreads;
     if (i < nvec) {
-      float w[8];
-      ld8(weight + i * 8, w);
+      const uint32_t wr[4] = {wraw[it].x, wraw[it].y, wraw[it].z, wraw[it].w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) y[it][e] = rnd<T>(__fmul_rn(__fmul_rn(y[it][e], inv), w[e]));
+      for (int e = 0; e < 4; ++e) {
+        const float2 w = unpack2<T>(wr[e]);
+        y[it][2 * e] = rnd<T>(__fmul_rn(__fmul_rn(y[it][2 * e], inv), w.x));
+        y[it][2 * e + 1] = rnd<T>(__fmul_rn(__fmul_rn(y[it][2 * e + 1], inv), w.y));
+      }
     }
   }
   emit_row<T>(y, nvec, m, o, red);
@@ -218,20 +264,26 @@ rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, i
 
 // ---- SiLU(gate) * up ------------------------------------------------------------------------------
 // activation.py:43-45: F.silu(x[..., :d]) * x[..., d:] on 16-bit tensors = T( T(silu(g)) * u )
+// Small token counts: the row is split over a cluster of gridDim.x / M CTAs (one CTA per row leaves
+// a 14336-wide row to 8 warps of one SM: 11 us at M = 1).
 template <typename T>
 __global__ void __launch_bounds__(kRowThreads)
-silu_mul_kernel(const T* __restrict__ x, int64_t ldx, int d, RowOut o) {
+silu_mul_kernel(const T* __restrict__ x, int64_t ldx, int d, int per, RowOut o) {
   __shared__ float red[32];
+  __shared__ float cl_slots[8];
+  const uint32_t S = cluster_size();
+  if (S > 1) cluster_barrier();  // every CTA of the cluster runs before any remote store is issued
   griddep_wait();
   griddep_launch_dependents();
-  const int m = blockIdx.x;
-  const int nvec = d / 8;
+  const int m = blockIdx.x / S;
+  const int i0 = static_cast<int>(cluster_rank()) * per;
+  const int nvec = min(d / 8, i0 + per);
   const T* grow = x + m * ldx;
   const T* urow = grow + d;
   float y[kMaxIters][8];
 #pragma unroll
   for (int it = 0; it < kMaxIters; ++it) {
-    const int i = threadIdx.x + it * kRowThreads;
+    const int i = i0 + threadIdx.x + it * kRowThreads;
     if (i < nvec) {
       float u[8];
       ld8(grow + i * 8, y[it]);
@@ -244,7 +296,7 @@ silu_mul_kernel(const T* __restrict__ x, int64_t ldx, int d, RowOut o) {
       }
     }
   }
-  emit_row<T>(y, nvec, m, o, red);
+  emit_row<T>(y, nvec, m, o, red, i0, S > 1 ? cl_slots : nullptr);
 }
 
 // ---- rotary embedding (+ KV-cache write) ------------------------------------------------------------
@@ -447,12 +499,17 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   {
     ScopedKernelTimer timer("silu_and_mul", st);
+    // cluster size: spread few rows over more SMs while every CTA keeps >= 256 vectors
+    const int nvec = d / 8;
+    int S = M <= 4 ? 8 : M <= 16 ? 4 : M <= 32 ? 2 : 1;
+    while (S > 1 && nvec < S * kRowThreads) S >>= 1;
+    const int per = ceil_div(ceil_div(nvec, S), 16) * 16;  // 128-groups stay inside one CTA
     if (dtype == B200_BF16)
-      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__nv_bfloat16>, dim3(M), dim3(kRowThreads), 0, st,
-                                 1, pdl_family(M, kPdlRow), static_cast<const __nv_bfloat16*>(x), ldx, d, o));
+      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__nv_bfloat16>, dim3(M * S), dim3(kRowThreads), 0, st,
+                                 S, pdl_family(M, kPdlRow), static_cast<const __nv_bfloat16*>(x), ldx, d, per, o));
     else
-      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__half>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
-                                 static_cast<const __half*>(x), ldx, d, o));
+      B200_CUDA_OK(launch_kernel(silu_mul_kernel<__half>, dim3(M * S), dim3(kRowThreads), 0, st, S, pdl_family(M, kPdlRow),
+                                 static_cast<const __half*>(x), ldx, d, per, o));
   }
   B200_CHECK_LAUNCH("silu_mul_kernel");
   return 0;
