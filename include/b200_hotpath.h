@@ -287,6 +287,18 @@ int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void
                        int native_rounding, void* k_cache, void* v_cache, int64_t cache_row_stride,
                        const int64_t* loc, int T, int Hq, int Hkv, int D, int dtype, void* stream);
 
+/* Same with an e4m3 KV pool (rows of bytes, cache_row_stride in bytes): the rotated k and v are
+ * quantised exactly as b200_kv_write_fp8 does (torch's float8_e4m3fn cast after the optional
+ * division by k_scale / v_scale, memory_pool.py:390-396; FlashInfer's set_kv_buffer call,
+ * flashinfer_backend.py:427), so one launch replaces RoPE + set_kv_buffer on an FP8 pool. */
+int b200_rope_kv_write_fp8(const int64_t* positions, void* q, int64_t q_stride, void* k,
+                           int64_t k_stride, const void* v, int64_t v_stride,
+                           const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
+                           int native_rounding, void* k_cache, void* v_cache,
+                           int64_t cache_row_stride, const int64_t* loc, float k_scale,
+                           float v_scale, int has_scale, int T, int Hq, int Hkv, int D, int dtype,
+                           void* stream);
+
 /* ---- tensor-parallel all-reduce over NVLink peer memory ------------------------------------- */
 /* Replaces the reference's custom all-reduce for decode-sized messages: host class CustomAllreduce
  * (python/sglang/srt/distributed/device_communicators/custom_all_reduce.py:146-510; buffers are

@@ -104,6 +104,10 @@ _SIGNATURES = {
                                    c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                    c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                    c_void_p]),
+    "b200_rope_kv_write_fp8": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                       c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                       c_void_p, c_int64, c_void_p, c_float, c_float, c_int, c_int,
+                                       c_int, c_int, c_int, c_int, c_void_p]),
     "b200_awq_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                  c_int, c_void_p]),
     "b200_w4a16_unpack_zeros": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,

@@ -212,4 +212,20 @@ __device__ __forceinline__ float to_float<__half>(__half x) {
   return __half2float(x);
 }
 
+// 16-bit float -> e4m3 byte with torch's `.to(torch.float8_e4m3fn)` semantics (round to nearest
+// even, NO saturation: |x| beyond the last value that still rounds to 448, i.e. > 464, and NaN/Inf
+// become NaN = sign | 0x7f), after the optional in-place `div_(scale)` of set_kv_buffer, whose
+// result is rounded back to the 16-bit dtype first (memory_pool.py:390-396).
+template <typename T>
+__device__ __forceinline__ uint32_t to_e4m3_torch(T x, float inv_is_div_scale, bool has_scale) {
+  float f = to_float<T>(x);
+  if (has_scale) f = to_float<T>(from_float<T>(f / inv_is_div_scale));
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(f));
+  uint32_t b = r & 0xffu;
+  if (!(fabsf(f) <= 464.f)) b = ((__float_as_uint(f) >> 24) & 0x80u) | 0x7fu;
+  return b;
+}
+
+
 }  // namespace b200

@@ -316,7 +316,40 @@ struct RopeParams {
   int64_t cache_row_stride;
   const int64_t* loc;
   int Hq, Hkv, D;
+  // e4m3 pool (b200_rope_kv_write_fp8): rows are bytes, values quantised as b200_kv_write_fp8 does
+  int cache_fp8;
+  float k_scale, v_scale;
+  int has_scale;
 };
+
+// 8 values (already rounded to T) into a cache row at element offset `off`
+template <typename T>
+__device__ __forceinline__ void st_cache8(const RopeParams& p, uint8_t* row, int off,
+                                          const float (&f)[8], float scale) {
+  if (p.cache_fp8) {
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      lo |= to_e4m3_torch<T>(from_float<T>(f[j]), scale, p.has_scale != 0) << (8 * j);
+      hi |= to_e4m3_torch<T>(from_float<T>(f[4 + j]), scale, p.has_scale != 0) << (8 * j);
+    }
+    *reinterpret_cast<uint2*>(row + off) = make_uint2(lo, hi);
+  } else {
+    st8(reinterpret_cast<T*>(row) + off, f);
+  }
+}
+// raw 16-bit chunk -> cache row (pass-through part of k, all of v)
+template <typename T>
+__device__ __forceinline__ void copy_cache8(const RopeParams& p, uint8_t* row, int off, const T* src,
+                                            float scale) {
+  if (p.cache_fp8) {
+    float f[8];
+    ld8(src, f);
+    st_cache8<T>(p, row, off, f, scale);
+  } else {
+    *reinterpret_cast<uint4*>(reinterpret_cast<T*>(row) + off) = *reinterpret_cast<const uint4*>(src);
+  }
+}
 
 template <typename T>
 __device__ __forceinline__ void load_cs(const RopeParams& p, int64_t pos, int j0, float (&c)[8],
@@ -373,8 +406,9 @@ rope_kv_write_kernel(const RopeParams p) {
   T* qrow = static_cast<T*>(p.q) + t * p.q_stride;
   T* krow = static_cast<T*>(p.k) + t * p.k_stride;
   const T* vrow = write ? static_cast<const T*>(p.v) + t * p.v_stride : nullptr;
-  T* kc = write ? static_cast<T*>(p.k_cache) + slot * p.cache_row_stride : nullptr;
-  T* vc = write ? static_cast<T*>(p.v_cache) + slot * p.cache_row_stride : nullptr;
+  const int esz = p.cache_fp8 ? 1 : static_cast<int>(sizeof(T));
+  uint8_t* kc = write ? static_cast<uint8_t*>(p.k_cache) + slot * p.cache_row_stride * esz : nullptr;
+  uint8_t* vc = write ? static_cast<uint8_t*>(p.v_cache) + slot * p.cache_row_stride * esz : nullptr;
   const int n_q = p.Hq * rot_items;
   const int n_k = p.Hkv * (write ? k_items : rot_items);
   const int n_v = write ? p.Hkv * cpd : 0;
@@ -382,7 +416,7 @@ rope_kv_write_kernel(const RopeParams p) {
   for (int w = threadIdx.x; w < n_q + n_k + n_v; w += blockDim.x) {
     if (w >= n_q + n_k) {  // v: plain copy into the cache
       const int c = w - n_q - n_k;
-      *reinterpret_cast<uint4*>(vc + c * 8) = *reinterpret_cast<const uint4*>(vrow + c * 8);
+      copy_cache8<T>(p, vc, c * 8, vrow + c * 8, p.v_scale);
       continue;
     }
     const bool is_k = w >= n_q;
@@ -390,10 +424,10 @@ rope_kv_write_kernel(const RopeParams p) {
     const int idx = is_k ? w - n_q : w;
     const int h = idx / per_head, it = idx - h * per_head;
     T* row = (is_k ? krow : qrow) + h * p.D;
-    T* crow = is_k && write ? kc + h * p.D : nullptr;
+    uint8_t* crow = is_k && write ? kc + h * p.D * esz : nullptr;
     if (it >= rot_items) {  // pass-through chunk of k
       const int c = p.rot / 8 + (it - rot_items);
-      *reinterpret_cast<uint4*>(crow + c * 8) = *reinterpret_cast<const uint4*>(row + c * 8);
+      copy_cache8<T>(p, crow, c * 8, row + c * 8, p.k_scale);
       continue;
     }
     if (p.is_neox) {
@@ -407,8 +441,8 @@ rope_kv_write_kernel(const RopeParams p) {
       st8(row + j0, o1);
       st8(row + p.rot / 2 + j0, o2);
       if (crow) {
-        st8(crow + j0, o1);
-        st8(crow + p.rot / 2 + j0, o2);
+        st_cache8<T>(p, crow, j0, o1, p.k_scale);
+        st_cache8<T>(p, crow, p.rot / 2 + j0, o2, p.k_scale);
       }
     } else {
       // gpt-j: elements (2j, 2j+1) of this chunk use cos/sin index j = it*4 + e
@@ -431,7 +465,7 @@ rope_kv_write_kernel(const RopeParams p) {
         rotate<T>(x[2 * e], x[2 * e + 1], c, s, native, o[2 * e], o[2 * e + 1]);
       }
       st8(row + it * 8, o);
-      if (crow) st8(crow + it * 8, o);
+      if (crow) st_cache8<T>(p, crow, it * 8, o, p.k_scale);
     }
   }
 }
@@ -515,11 +549,13 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
   return 0;
 }
 
-int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void* k,
-                       int64_t k_stride, const void* v, int64_t v_stride,
-                       const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
-                       int native_rounding, void* k_cache, void* v_cache, int64_t cache_row_stride,
-                       const int64_t* loc, int T, int Hq, int Hkv, int D, int dtype, void* stream) {
+static int rope_kv_write_impl(const int64_t* positions, void* q, int64_t q_stride, void* k,
+                              int64_t k_stride, const void* v, int64_t v_stride,
+                              const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
+                              int native_rounding, void* k_cache, void* v_cache,
+                              int64_t cache_row_stride, const int64_t* loc, int cache_fp8,
+                              float k_scale, float v_scale, int has_scale, int T, int Hq, int Hkv,
+                              int D, int dtype, void* stream) {
   using namespace b200;
   if (T == 0) return 0;
   B200_REQUIRE(positions && q && k && cos_sin_cache, "b200_rope_kv_write: null pointer");
@@ -538,7 +574,7 @@ int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void
                "b200_rope_kv_write: pointers must be 16-byte aligned with strides %% 8 == 0");
   RopeParams p{positions, q, q_stride, k, k_stride, v, v_stride, cos_sin_cache,
                cache_dtype == B200_F32 ? 1 : 0, rotary_dim, is_neox, native_rounding, k_cache,
-               v_cache, cache_row_stride, loc, Hq, Hkv, D};
+               v_cache, cache_row_stride, loc, Hq, Hkv, D, cache_fp8, k_scale, v_scale, has_scale};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   {
     ScopedKernelTimer timer("rope_kv_write", st);
@@ -549,6 +585,32 @@ int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void
   }
   B200_CHECK_LAUNCH("rope_kv_write_kernel");
   return 0;
+}
+
+int b200_rope_kv_write(const int64_t* positions, void* q, int64_t q_stride, void* k,
+                       int64_t k_stride, const void* v, int64_t v_stride,
+                       const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
+                       int native_rounding, void* k_cache, void* v_cache, int64_t cache_row_stride,
+                       const int64_t* loc, int T, int Hq, int Hkv, int D, int dtype, void* stream) {
+  return rope_kv_write_impl(positions, q, q_stride, k, k_stride, v, v_stride, cos_sin_cache,
+                            cache_dtype, rotary_dim, is_neox, native_rounding, k_cache, v_cache,
+                            cache_row_stride, loc, 0, 1.f, 1.f, 0, T, Hq, Hkv, D, dtype, stream);
+}
+
+int b200_rope_kv_write_fp8(const int64_t* positions, void* q, int64_t q_stride, void* k,
+                           int64_t k_stride, const void* v, int64_t v_stride,
+                           const void* cos_sin_cache, int cache_dtype, int rotary_dim, int is_neox,
+                           int native_rounding, void* k_cache, void* v_cache,
+                           int64_t cache_row_stride, const int64_t* loc, float k_scale,
+                           float v_scale, int has_scale, int T, int Hq, int Hkv, int D, int dtype,
+                           void* stream) {
+  B200_REQUIRE(k_cache && v_cache, "b200_rope_kv_write_fp8: the e4m3 pool rows are required");
+  B200_REQUIRE(!has_scale || (k_scale > 0.f && v_scale > 0.f),
+               "b200_rope_kv_write_fp8: scales must be positive");
+  return rope_kv_write_impl(positions, q, q_stride, k, k_stride, v, v_stride, cos_sin_cache,
+                            cache_dtype, rotary_dim, is_neox, native_rounding, k_cache, v_cache,
+                            cache_row_stride, loc, 1, k_scale, v_scale, has_scale, T, Hq, Hkv, D,
+                            dtype, stream);
 }
 
 }  // extern "C"

@@ -172,3 +172,51 @@ def test_rope_fused_kv_write_bit_exact(hq, hkv, d, rot, neox, dtype):
     untouched[loc] = False
     assert (kb[untouched] == 3.0).all() and (vb[untouched] == -2.0).all()
     assert (pool.k_buffer[0] == 0).all()
+
+
+@pytest.mark.parametrize("hq,hkv,d,rot,neox", [(32, 8, 128, 128, True), (8, 8, 128, 64, False),
+                                               (14, 2, 64, 64, True)])
+@pytest.mark.parametrize("scales", [None, (0.37, 2.5)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rope_fused_fp8_kv_write_matches_unfused_bytes(hq, hkv, d, rot, neox, scales, dtype):
+    """e4m3 pool: the one-launch RoPE + quantising scatter writes the bytes that RoPE followed by
+    set_kv_buffer (b200_kv_write_fp8, itself pinned to torch's div_ -> .to(float8_e4m3fn) in
+    test_fp8_kv_gpu.py) writes, including out-of-range values (NaN code) and untouched rows."""
+    from types import SimpleNamespace
+
+    from sglang_security_b200.layers.rotary_embedding import RotaryEmbedding
+    from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool
+
+    g = torch.Generator().manual_seed(hq + d + (0 if scales is None else 5))
+    t, max_pos, pool_size = 41, 2048, 150
+    qkv = (torch.randn(t, (hq + 2 * hkv) * d, generator=g) * 3).to(dtype)
+    qkv[3, hq * d + 5] = 700.0          # beyond e4m3 range in k
+    qkv[7, (hq + hkv) * d + 9] = -900.0  # and in v
+    pos = torch.randint(0, max_pos, (t,), generator=g)
+    loc = (torch.randperm(pool_size, generator=g)[:t] + 1).to(torch.int64).cuda()
+    rope = RotaryEmbedding(d, rot, max_pos, 10000.0, neox, dtype, native_rounding=True).cuda()
+    layer = SimpleNamespace(layer_id=0)
+    if scales is not None:
+        layer.k_scale_float, layer.v_scale_float = scales
+
+    def run(fused):
+        pool = MHATokenToKVPool(pool_size, 1, torch.float8_e4m3fn, hkv, d, 1, "cuda")
+        pool.k_buffer[0].view(torch.uint8).fill_(0x11)
+        pool.v_buffer[0].view(torch.uint8).fill_(0x22)
+        dq = qkv.cuda().clone()
+        q, k, v = dq.split([hq * d, hkv * d, hkv * d], dim=-1)
+        if fused:
+            fb = SimpleNamespace(token_to_kv_pool=pool, out_cache_loc=loc)
+            rope.forward_with_kv_write(pos.cuda(), q, k, v, layer, fb)
+        else:
+            rope(pos.cuda(), q, k)
+            ks, vs = scales if scales is not None else (None, None)
+            pool.set_kv_buffer(layer, loc, k.reshape(t, hkv, d), v.reshape(t, hkv, d), ks, vs)
+        return (q.clone(), k.clone(), pool.k_buffer[0].view(torch.uint8).clone(),
+                pool.v_buffer[0].view(torch.uint8).clone())
+
+    qa, ka, kba, vba = run(True)
+    qb, kb, kbb, vbb = run(False)
+    assert torch.equal(qa, qb) and torch.equal(ka, kb)
+    assert torch.equal(kba, kbb) and torch.equal(vba, vbb)
+    assert (kba[loc.cpu()] != 0x11).any() and (kba[0] == 0x11).all() and (vba[0] == 0x22).all()
