@@ -177,8 +177,11 @@ class RowParallelLinear(LinearBase):
             comm = get_tp_custom_all_reduce()
             # the peer-memory path (fused epilogue or stand-alone one-shot kernel, chosen inside the
             # library) only up to the measured crossover with NCCL for this group size
-            tokens = input_.numel() // max(1, input_.shape[-1])
-            out_bytes = tokens * self.output_size * input_.element_size()
+            # (input_ may be a QuantizedActivation: only .shape and .dtype = the output dtype)
+            tokens = 1
+            for dim in input_.shape[:-1]:
+                tokens *= int(dim)
+            out_bytes = tokens * self.output_size * input_.dtype.itemsize
             if (comm is not None and out_bytes <= getattr(comm, "crossover", 0)
                     and getattr(self.quant_method, "supports_fused_all_reduce", False)):
                 # GEMM -> all-reduce as one call: the decode-regime kernel reduces in its epilogue

@@ -236,6 +236,14 @@ def _mp_worker(rank, world, port, out_dir):
             parts = [torch.empty_like(part) for _ in range(world)]
             dist.all_gather(parts, part)
             assert torch.equal(y.cpu(), OA.row_parallel_linear_oracle(parts)), (fuse_max, m)
+            # an activation quantised by its producer (fused RMSNorm / SiLU*mul -> quant) takes the
+            # same path and gives the same bytes
+            from sglang_security_b200.layers.quantization.fp8_kernel import sglang_per_token_quant_fp8
+            from sglang_security_b200.layers.quantization.fp8_utils import QuantizedActivation
+
+            xq, xs = sglang_per_token_quant_fp8(x)
+            yq, _ = layer(QuantizedActivation(xq, xs, torch.bfloat16))
+            assert torch.equal(yq, y), ("quantised input", fuse_max, m)
         # block-scaled kernel: fused (M <= 64) and big tile + stand-alone all-reduce (M = 150)
         k = 1024
         wq = ((torch.rand((hidden, k), generator=g) - 0.5) * 8).to(FP8).cuda()
