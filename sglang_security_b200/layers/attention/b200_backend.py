@@ -14,8 +14,8 @@ decode step can be captured in a CUDA graph.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass
-from typing import Optional
+from dataclasses import dataclass, field
+from typing import Dict, Optional
 
 import torch
 
@@ -32,10 +32,20 @@ class ForwardMetadata:
     qo_indptr: Optional[torch.Tensor] = None
     max_extend_len: int = 0
     total_extend: int = 0
+    # dtype-converted copies of the ForwardBatch index tensors, kept alive for the whole forward
+    # (one conversion per step, never a temporary whose block the allocator could hand out again
+    # before the launch has read it); keyed by (data_ptr, dtype, numel) of the source
+    converted: Dict[tuple, torch.Tensor] = field(default_factory=dict)
 
-
-def _as_i64(t: torch.Tensor) -> torch.Tensor:
-    return t if t.dtype == torch.int64 else t.to(torch.int64)
+    def as_dtype(self, t: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+        if t.dtype == dtype:
+            return t
+        key = (t.data_ptr(), t.dtype, dtype, t.numel())
+        out = self.converted.get(key)
+        if out is None:
+            out = t.to(dtype)
+            self.converted[key] = out
+        return out
 
 
 class B200AttnBackend(AttentionBackend):
@@ -117,6 +127,20 @@ class B200AttnBackend(AttentionBackend):
         need = self.lib.b200_attn_decode_workspace_bytes(max_bs, self.num_head, self.v_head_dim,
                                                          max_splits)
         self._graph_workspace = torch.empty(max(need, 16), dtype=torch.uint8, device=self.device)
+        # int64 staging for runners that keep req_pool_indices / seq_lens as int32
+        # (cuda_graph_runner.py:250-253): refreshed by the replay hook, read by the captured kernels
+        self._graph_index = {n: torch.zeros(max_bs, dtype=torch.int64, device=self.device)
+                             for n in ("req_pool_indices", "seq_lens")}
+
+    def _stage_graph_indices(self, md, bs, req_pool_indices, seq_lens):
+        for name, t in (("req_pool_indices", req_pool_indices), ("seq_lens", seq_lens)):
+            if t is None or t.dtype == torch.int64:
+                continue
+            t = t[:bs]
+            buf = self._graph_index[name][:bs]
+            buf.copy_(t)
+            if md is not None:
+                md.converted[(t.data_ptr(), t.dtype, torch.int64, t.numel())] = buf
 
     def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens,
                                                  encoder_lens, forward_mode, spec_info):
@@ -127,13 +151,15 @@ class B200AttnBackend(AttentionBackend):
         # The split count is frozen into the captured launch: choose it for a nominal context.
         s = min(64, self._num_splits(bs, self.v_head_dim, min(self.max_context_len, 4096)))
         self.forward_metadata = ForwardMetadata(num_splits=s, workspace=self._graph_workspace)
+        self._stage_graph_indices(self.forward_metadata, bs, req_pool_indices, seq_lens)
 
     def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum,
                                                 encoder_lens, forward_mode, spec_info,
                                                 seq_lens_cpu):
-        # Nothing to refresh: the decode kernel reads req_to_token / seq_lens directly, so there
-        # is no derived index buffer to rebuild and no host sync.
-        return
+        # The decode kernel reads req_to_token / seq_lens directly, so there is no derived index
+        # buffer to rebuild and no host sync; only int32 index tensors are widened into the
+        # persistent int64 staging the captured launches point at (two tiny async copies).
+        self._stage_graph_indices(None, bs, req_pool_indices, seq_lens)
 
     def get_cuda_graph_seq_len_fill_value(self):
         return 1
@@ -158,11 +184,26 @@ class B200AttnBackend(AttentionBackend):
         are radix_attention.py:74-75)."""
         ks = getattr(layer, "k_scale_float", None)
         vs = getattr(layer, "v_scale_float", None)
+        # float(tensor) is a device sync and cannot be captured in a CUDA graph: read each scale
+        # once (the reference fills k_scale_float at load time, radix_attention.py:74-75) and cache
         if ks is None and layer.k_scale is not None:
-            ks = float(layer.k_scale)
+            ks = layer.k_scale_float = float(layer.k_scale)
         if vs is None and layer.v_scale is not None:
-            vs = float(layer.v_scale)
+            vs = layer.v_scale_float = float(layer.v_scale)
         return ks, vs
+
+    @staticmethod
+    def _check_layer(layer):
+        """Features of the reference's Triton backend that this backend does not implement must
+        fail loudly instead of silently running full self-attention (triton_backend.py:271-446
+        handles the window; cross-attention indexes encoder rows)."""
+        window = getattr(layer, "sliding_window_size", None)
+        if window is not None and window > 0:
+            raise NotImplementedError(
+                f"B200AttnBackend: sliding_window_size={window} is not implemented "
+                "(no BASELINE config uses a window)")
+        if getattr(layer, "is_cross_attention", False):
+            raise NotImplementedError("B200AttnBackend: cross-attention layers are not implemented")
 
     def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
         hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
@@ -180,16 +221,21 @@ class B200AttnBackend(AttentionBackend):
             v_cache = pool.get_value_buffer(layer.layer_id)
         if bs == 0:
             return o
+        self._check_layer(layer)
         md = self.forward_metadata
         req_to_token = forward_batch.req_to_token_pool.req_to_token
         ws = md.workspace
+        # the reference's CudaGraphRunner keeps these as int32 (cuda_graph_runner.py:250-253); the
+        # kernels read int64, so convert once per forward and hold the copies in the metadata
+        req_pool_indices = md.as_dtype(forward_batch.req_pool_indices, torch.int64)
+        seq_lens = md.as_dtype(forward_batch.seq_lens, torch.int64)
         if k_cache.dtype == torch.float8_e4m3fn:
             ks, vs = self._kv_scales(layer)
             rc = self.lib.b200_attn_decode_fp8kv(
                 q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
                 k_cache.stride(0), o.data_ptr(), o.stride(0), req_to_token.data_ptr(),
-                req_to_token.stride(0), _as_i64(forward_batch.req_pool_indices).data_ptr(),
-                _as_i64(forward_batch.seq_lens).data_ptr(), bs, hq, hkv, d, dv,
+                req_to_token.stride(0), req_pool_indices.data_ptr(),
+                seq_lens.data_ptr(), bs, hq, hkv, d, dv,
                 float(layer.scaling), float(layer.logit_cap or 0.0),
                 1.0 if ks is None else ks, 1.0 if vs is None else vs, _lib.dtype_code(q.dtype),
                 _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits,
@@ -203,8 +249,7 @@ class B200AttnBackend(AttentionBackend):
         rc = self.lib.b200_attn_decode(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
             o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
-            _as_i64(forward_batch.req_pool_indices).data_ptr(),
-            _as_i64(forward_batch.seq_lens).data_ptr(), bs, hq, hkv, d, dv,
+            req_pool_indices.data_ptr(), seq_lens.data_ptr(), bs, hq, hkv, d, dv,
             float(layer.scaling), float(layer.logit_cap or 0.0), _lib.dtype_code(q.dtype),
             _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits, _lib.current_stream())
         _lib.check(rc, "b200_attn_decode")
@@ -233,8 +278,11 @@ class B200AttnBackend(AttentionBackend):
         causal = not (layer.is_cross_attention or
                       getattr(attn_type, "value", attn_type) == "encoder_only")
         req_to_token = forward_batch.req_to_token_pool.req_to_token
-        req_pool_indices = _as_i64(forward_batch.req_pool_indices)
-        seq_lens = _as_i64(forward_batch.seq_lens)
+        self._check_layer(layer)
+        req_pool_indices = md.as_dtype(forward_batch.req_pool_indices, torch.int64)
+        seq_lens = md.as_dtype(forward_batch.seq_lens, torch.int64)
+        prefix_lens = md.as_dtype(forward_batch.extend_prefix_lens, torch.int32)
+        extend_lens = md.as_dtype(forward_batch.extend_seq_lens, torch.int32)
         scaling, out_scale = float(layer.scaling), 1.0
         if k_cache.dtype == torch.float8_e4m3fn:
             # FP8 pool: the tcgen05 kernel wants 16-bit operands, so the requests' rows are first
@@ -253,8 +301,7 @@ class B200AttnBackend(AttentionBackend):
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
             o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
             req_pool_indices.data_ptr(), seq_lens.data_ptr(),
-            forward_batch.extend_prefix_lens.to(torch.int32).data_ptr(),
-            forward_batch.extend_seq_lens.to(torch.int32).data_ptr(), md.qo_indptr.data_ptr(), bs,
+            prefix_lens.data_ptr(), extend_lens.data_ptr(), md.qo_indptr.data_ptr(), bs,
             md.max_extend_len, hq, hkv, d, dv, scaling, float(layer.logit_cap or 0.0), out_scale,
             1 if causal else 0, _lib.dtype_code(q.dtype), _lib.current_stream())
         _lib.check(rc, "b200_attn_extend")

@@ -36,10 +36,13 @@ def write_req_to_token_pool(req_to_token: torch.Tensor, req_pool_indices: torch.
     if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
         raise _lib.B200Error("write_req_to_token_pool: req_to_token must be int32, row-major")
     bs = req_pool_indices.numel()
+    # converted copies are bound to locals: a temporary would be freed (and its block handed to the
+    # next conversion) before the launch reads it
+    rpi, pre, seq, ext, loc = (_i64(req_pool_indices), _i64(pre_lens), _i64(seq_lens),
+                               _i64(extend_lens), _i64(out_cache_loc))
     rc = _lib.load().b200_write_req_to_token(
-        req_to_token.data_ptr(), req_to_token.stride(0), _i64(req_pool_indices).data_ptr(),
-        _i64(pre_lens).data_ptr(), _i64(seq_lens).data_ptr(), _i64(extend_lens).data_ptr(),
-        _i64(out_cache_loc).data_ptr(), bs, _lib.current_stream())
+        req_to_token.data_ptr(), req_to_token.stride(0), rpi.data_ptr(), pre.data_ptr(),
+        seq.data_ptr(), ext.data_ptr(), loc.data_ptr(), bs, _lib.current_stream())
     _lib.check(rc, "b200_write_req_to_token")
 
 
@@ -48,9 +51,10 @@ def get_last_loc(req_to_token: torch.Tensor, req_pool_indices_tensor: torch.Tens
     _need_cuda(req_to_token, "get_last_loc")
     n = prefix_lens_tensor.numel()
     result = torch.empty(n, dtype=torch.int64, device=req_to_token.device)
+    rpi, pre = _i64(req_pool_indices_tensor), _i64(prefix_lens_tensor)
     rc = _lib.load().b200_get_last_loc(
-        req_to_token.data_ptr(), req_to_token.stride(0), _i64(req_pool_indices_tensor).data_ptr(),
-        _i64(prefix_lens_tensor).data_ptr(), result.data_ptr(), n, _lib.current_stream())
+        req_to_token.data_ptr(), req_to_token.stride(0), rpi.data_ptr(), pre.data_ptr(),
+        result.data_ptr(), n, _lib.current_stream())
     _lib.check(rc, "b200_get_last_loc")
     return result.to(prefix_lens_tensor.dtype)
 
@@ -65,9 +69,10 @@ def compute_position(extend_prefix_lens: Optional[torch.Tensor], extend_seq_lens
     start = torch.empty(bs, dtype=torch.int32, device=dev)
     has_prefix = extend_prefix_lens is not None and extend_prefix_lens.numel() == bs
     pre = extend_prefix_lens.to(torch.int32) if has_prefix else None
+    ext = extend_seq_lens.to(torch.int32)
     rc = _lib.load().b200_compute_position(
-        positions.data_ptr(), start.data_ptr(), _lib.ptr(pre),
-        extend_seq_lens.to(torch.int32).data_ptr(), bs, _lib.current_stream())
+        positions.data_ptr(), start.data_ptr(), _lib.ptr(pre), ext.data_ptr(), bs,
+        _lib.current_stream())
     _lib.check(rc, "b200_compute_position")
     return positions, start
 
@@ -106,8 +111,9 @@ class PagedTokenToKVPoolAllocator:
                      last_loc: torch.Tensor, extend_num_tokens: int):
         bs = len(prefix_lens)
         out_indices = torch.empty((extend_num_tokens,), dtype=torch.int64, device=self.device)
+        pre, seq, last = _i64(prefix_lens), _i64(seq_lens), _i64(last_loc)
         rc = _lib.load().b200_alloc_extend(
-            _i64(prefix_lens).data_ptr(), _i64(seq_lens).data_ptr(), _i64(last_loc).data_ptr(),
+            pre.data_ptr(), seq.data_ptr(), last.data_ptr(),
             self.free_pages.data_ptr(), out_indices.data_ptr(), self.ret_values.data_ptr(), bs,
             self.page_size, _lib.current_stream())
         _lib.check(rc, "b200_alloc_extend")
@@ -121,8 +127,9 @@ class PagedTokenToKVPoolAllocator:
     def alloc_decode(self, seq_lens: torch.Tensor, last_loc: torch.Tensor):
         bs = len(seq_lens)
         out_indices = torch.empty((bs,), dtype=torch.int64, device=self.device)
+        seq, last = _i64(seq_lens), _i64(last_loc)
         rc = _lib.load().b200_alloc_decode(
-            _i64(seq_lens).data_ptr(), _i64(last_loc).data_ptr(), self.free_pages.data_ptr(),
+            seq.data_ptr(), last.data_ptr(), self.free_pages.data_ptr(),
             out_indices.data_ptr(), self.ret_values.data_ptr(), bs, self.page_size,
             _lib.current_stream())
         _lib.check(rc, "b200_alloc_decode")

@@ -48,7 +48,7 @@ def make_model_runner(case, device="cuda", layer_num=1, num_kv_splits=0):
                            server_args=SimpleNamespace(b200_attention_num_kv_splits=num_kv_splits))
 
 
-def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True):
+def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype=None):
     """CUDA path: B200AttnBackend through RadixAttention.forward, KV write included."""
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
     from sglang_security_b200.layers.radix_attention import RadixAttention
@@ -68,8 +68,12 @@ def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True):
         q, k, v = case.q.to(dev), case.k_new.to(dev).reshape(t, -1), case.v_new.to(dev).reshape(t, -1)
     fb = ForwardBatch(
         forward_mode=ForwardMode.DECODE if case.decode else ForwardMode.EXTEND,
-        batch_size=case.bs, req_pool_indices=case.req_pool_indices.to(dev),
-        seq_lens=case.seq_lens.to(dev), out_cache_loc=case.out_cache_loc.to(dev),
+        batch_size=case.bs,
+        # index_dtype=torch.int32 is what the reference's CudaGraphRunner hands the backend
+        # (cuda_graph_runner.py:250-253); the default keeps the ForwardBatch's int64
+        req_pool_indices=case.req_pool_indices.to(dev).to(index_dtype or torch.int64),
+        seq_lens=case.seq_lens.to(dev).to(index_dtype or torch.int64),
+        out_cache_loc=case.out_cache_loc.to(dev),
         seq_lens_sum=int(case.seq_lens.sum()), seq_lens_cpu=case.seq_lens,
         extend_seq_lens=case.extend_seq_lens.to(dev),
         extend_prefix_lens=case.extend_prefix_lens.to(dev),

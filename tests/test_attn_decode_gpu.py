@@ -81,7 +81,19 @@ def test_decode_logit_cap():
     _check(case, num_kv_splits=2, logit_cap=30.0)
 
 
-def test_decode_cuda_graph_capture_and_replay():
+def test_decode_int32_index_tensors():
+    """req_pool_indices / seq_lens as int32 (what the reference's CudaGraphRunner allocates,
+    cuda_graph_runner.py:250-253): the converted copies must stay alive until the launch — both are
+    bs*8 bytes, so a freed temporary of the first would be overwritten by the second."""
+    for lens in ([1, 63, 300, 1025, 700], [4097, 2500, 77]):
+        case = scenarios.make_attention_case(seed=41, hq=32, hkv=8, d=128, seq_lens=lens)
+        # request slots deliberately != lengths so a swapped pointer cannot pass by accident
+        for splits in (0, 3):
+            _check(case, num_kv_splits=splits, index_dtype=torch.int32)
+
+
+@pytest.mark.parametrize("index_dtype", [torch.int64, torch.int32])
+def test_decode_cuda_graph_capture_and_replay(index_dtype):
     """Decode step captured once, replayed after req_to_token / seq_lens / q change in place."""
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
     from sglang_security_b200.layers.radix_attention import RadixAttention
@@ -105,8 +117,8 @@ def test_decode_cuda_graph_capture_and_replay():
     q = case_a.q.to(dev)
     k = case_a.k_new.to(dev)
     v = case_a.v_new.to(dev)
-    req_pool_indices = case_a.req_pool_indices.to(dev)
-    seq_lens = case_a.seq_lens.to(dev)
+    req_pool_indices = case_a.req_pool_indices.to(dev).to(index_dtype)
+    seq_lens = case_a.seq_lens.to(dev).to(index_dtype)
     out_cache_loc = case_a.out_cache_loc.to(dev)
     fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=bs,
                       req_pool_indices=req_pool_indices, seq_lens=seq_lens,

@@ -71,3 +71,26 @@ def test_extend_large_magnitude_scores_rescale():
     o, _, _ = harness.b200_run(case)
     st = harness.error_stats(o, o_ref)
     assert st["rel_l2"] <= 2e-2, st
+
+
+def test_extend_int32_index_tensors():
+    """int32 req_pool_indices / seq_lens (cuda_graph_runner.py:250-253 convention): converted copies
+    are held in the metadata for the whole forward, never as temporaries."""
+    case = scenarios.make_attention_case(seed=80, hq=8, hkv=2, d=128, seq_lens=[700, 64, 65, 300],
+                                         extend_lens=[129, 64, 1, 300])
+    _check(case, index_dtype=torch.int32)
+
+
+def test_extend_8k_context_llama_heads():
+    """cfg-3/5 chunk shape at the size the perf numbers are quoted on: 512 new tokens after a 7680-
+    token cached prefix (8k context), Llama-3.1-8B heads, and a radix-hit-0.9 request."""
+    case = scenarios.make_attention_case(seed=81, hq=32, hkv=8, d=128, seq_lens=[8192, 2048],
+                                         extend_lens=[512, 205])
+    _check(case)
+
+
+def test_extend_tp8_rank_geometry():
+    """Llama-3.1-70B at TP=8: a rank holds Hq 8 / Hkv 1 (one GQA group fills the whole M tile)."""
+    case = scenarios.make_attention_case(seed=82, hq=8, hkv=1, d=128, seq_lens=[8192, 1024, 130],
+                                         extend_lens=[1024, 1024, 1])
+    _check(case)

@@ -46,6 +46,41 @@ def test_write_req_to_token_bit_exact(bs):
     assert torch.equal(dev.cpu(), ref)
 
 
+def test_index_helpers_accept_int32_inputs():
+    """int32 index tensors (the dtype the reference's scheduler uses for seq_lens / prefix lens on
+    some paths): every converted copy must outlive its launch — five same-sized conversions in a row
+    used to land in the same allocator block."""
+    from sglang_security_b200.mem_cache.paged_allocator import (PagedTokenToKVPoolAllocator,
+                                                                get_last_loc,
+                                                                write_req_to_token_pool)
+
+    g = torch.Generator().manual_seed(3)
+    bs, ctx = 48, 700
+    pre = torch.randint(0, 300, (bs,), generator=g)
+    ext = torch.randint(1, 400, (bs,), generator=g)
+    seq = pre + ext
+    rpi = torch.randperm(bs + 5, generator=g)[:bs]
+    loc = torch.randint(1, 1 << 30, (int(ext.sum()),), generator=g)
+    table = torch.randint(0, 100, (bs + 5, ctx), generator=g, dtype=torch.int32)
+    ref = O.write_req_to_token_oracle(table.clone(), rpi, pre, seq, ext, loc)
+    i32 = lambda t: t.to(torch.int32).cuda()
+    dev = table.cuda()
+    write_req_to_token_pool(dev, i32(rpi), i32(pre), i32(seq), i32(ext), loc.cuda())
+    assert torch.equal(dev.cpu(), ref)
+    last = get_last_loc(dev, i32(rpi), i32(pre))
+    last_ref = get_last_loc(dev, rpi.cuda(), pre.cuda())
+    assert torch.equal(last.cpu().long(), last_ref.cpu())
+    for page in (16, 64):
+        a32 = PagedTokenToKVPoolAllocator(64 * 1024, page, torch.bfloat16, "cuda")
+        a64 = PagedTokenToKVPoolAllocator(64 * 1024, page, torch.bfloat16, "cuda")
+        out32 = a32.alloc_extend(i32(pre), i32(seq), i32(last_ref), int(ext.sum()))
+        out64 = a64.alloc_extend(pre.cuda(), seq.cuda(), last_ref, int(ext.sum()))
+        assert torch.equal(out32, out64) and torch.equal(a32.free_pages, a64.free_pages)
+        d32 = a32.alloc_decode(i32(seq + 1), i32(last_ref))
+        d64 = a64.alloc_decode((seq + 1).cuda(), last_ref)
+        assert torch.equal(d32, d64) and torch.equal(a32.free_pages, a64.free_pages)
+
+
 @pytest.mark.parametrize("page", [1, 16, 64])
 def test_paged_allocator_extend_then_decode(page):
     from sglang_security_b200.mem_cache.paged_allocator import (PagedTokenToKVPoolAllocator,
