@@ -1,7 +1,7 @@
 """Compile the reference's own CPU attention kernels into oracle/_ref/ (authoring container only).
 
 TEST INFRASTRUCTURE ONLY.  Sources are compiled WHERE THEY LIE under /root/reference
-(sgl-kernel/csrc/cpu/decode.cpp, extend.cpp + headers); nothing is copied into this repo.  Only
+(sgl-kernel/csrc/cpu/decode.cpp, extend.cpp, gemm.cpp, gemm_fp8.cpp + headers); nothing is copied into this repo.  Only
 the outputs (two .so files and build_info.json) land in oracle/_ref/, which is git-ignored but
 travels to the GPU box.  Two ISA variants are built because the GPU box's host CPU may differ:
   native  : -march=native of the authoring container (AVX512-BF16 + AMX kernels, the reference's
@@ -23,6 +23,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
 REF_CPU = os.path.join(os.environ.get("B200_REFERENCE_ROOT", "/root/reference"), "sgl-kernel", "csrc",
                        "cpu")
+# decode/extend attention + the W8A16 block-FP8 linear (fp8_scaled_mm_cpu) and its weight pre-pack
+REF_SOURCES = ("decode.cpp", "extend.cpp", "gemm.cpp", "gemm_fp8.cpp")
 ISA_FLAGS = ("avx2", "fma", "avx512f", "avx512bw", "avx512vl", "avx512dq", "avx512_bf16",
              "avx512_vnni", "amx_tile", "amx_bf16", "amx_int8", "avx512_fp16")
 
@@ -53,8 +55,7 @@ def _compile(variant: str, march: str) -> str:
            f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
            "-I", REF_CPU, "-I", os.path.join(ref_root, "include"), "-I", os.path.join(ref_root, "csrc"),
            *inc,
-           os.path.join(HERE, "ref_shim.cpp"), os.path.join(REF_CPU, "decode.cpp"),
-           os.path.join(REF_CPU, "extend.cpp"),
+           os.path.join(HERE, "ref_shim.cpp"), *[os.path.join(REF_CPU, f) for f in REF_SOURCES],
            "-o", out, f"-L{torch_lib}", "-ltorch", "-ltorch_cpu", "-lc10", "-l:libgomp.so.1",
            f"-Wl,-rpath,{torch_lib}"]
     res = subprocess.run(cmd, capture_output=True, text=True)
@@ -68,8 +69,8 @@ def build(force: bool = False):
         return None  # GPU box: only the prebuilt files are used
     os.makedirs(OUT, exist_ok=True)
     info_path = os.path.join(OUT, "build_info.json")
-    srcs = [os.path.join(HERE, "ref_shim.cpp"), os.path.join(REF_CPU, "decode.cpp"),
-            os.path.join(REF_CPU, "extend.cpp"), os.path.abspath(__file__)]
+    srcs = [os.path.join(HERE, "ref_shim.cpp"), *[os.path.join(REF_CPU, f) for f in REF_SOURCES],
+            os.path.abspath(__file__)]
     newest = max(os.path.getmtime(s) for s in srcs)
     outs = [os.path.join(OUT, f"libsgl_cpu_ref_{v}.so") for v in ("native", "generic")]
     if (not force and os.path.exists(info_path)
@@ -79,7 +80,7 @@ def build(force: bool = False):
         list(ex.map(lambda a: _compile(*a), [("native", "native"), ("generic", "x86-64-v3")]))
     flags = cpu_flags()
     json.dump({"native_required_flags": sorted(f for f in ISA_FLAGS if f in flags),
-               "sources": ["sgl-kernel/csrc/cpu/decode.cpp", "sgl-kernel/csrc/cpu/extend.cpp"],
+               "sources": [f"sgl-kernel/csrc/cpu/{f}" for f in REF_SOURCES],
                "compiler": "g++ -O3 -fopenmp"}, open(info_path, "w"), indent=1)
     return OUT
 

@@ -58,3 +58,16 @@ def decode_attention_ref(q, k_cache, v_cache, k_new, v_new, loc, req_to_token, r
                              req_to_token, req_pool_indices, seq_lens, float(sm_scale),
                              float(logit_cap))
     return o
+
+
+def fp8_linear_prepack(weight_fp8):
+    """One-time VNNI pre-pack of an e4m3 weight [N, K] (convert_weight_packed, gemm.cpp:401-464);
+    the reference CPU path does this at load time (is_vnni=True afterwards)."""
+    return load().convert_weight_packed(weight_fp8)
+
+
+def fp8_scaled_mm_ref(x, packed_weight, scales, block=(128, 128), bias=None):
+    """The reference's CPU FP8 linear: x [M, K] bf16/f16 x e4m3 weight [N, K] with block scales
+    [ceil(N/bn), ceil(K/bk)] fp32 -> [M, N] in x.dtype (fp8_scaled_mm_cpu, gemm_fp8.cpp:480-545:
+    W8A16 — the activation stays 16-bit on the CPU path)."""
+    return load().fp8_scaled_mm_cpu(x, packed_weight, scales, list(block), bias, x.dtype, True)

@@ -85,6 +85,17 @@ def tensor_model_parallel_all_gather(input_: torch.Tensor, dim: int = -1) -> tor
         return input_
     if dim < 0:
         dim += input_.dim()
+    input_ = input_.contiguous()
+    if input_.is_cuda:
+        # one flat collective into [tp, ...] then a single reshuffle (GroupCoordinator.all_gather,
+        # parallel_state.py:463-500) — capturable in a CUDA graph
+        out = torch.empty((_TP_SIZE,) + tuple(input_.shape), dtype=input_.dtype,
+                          device=input_.device)
+        dist.all_gather_into_tensor(out, input_, group=_TP_GROUP)
+        out = out.movedim(0, dim)
+        shape = list(input_.shape)
+        shape[dim] *= _TP_SIZE
+        return out.reshape(shape)
     parts = [torch.empty_like(input_) for _ in range(_TP_SIZE)]
-    dist.all_gather(parts, input_.contiguous(), group=_TP_GROUP)
+    dist.all_gather(parts, input_, group=_TP_GROUP)
     return torch.cat(parts, dim=dim)
