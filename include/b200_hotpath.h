@@ -35,6 +35,11 @@ enum b200_dtype {
 int b200_version(void);
 /* Thread-local text of the last error raised by a b200_* call in this thread. */
 const char* b200_last_error(void);
+/* Test hook: thread-local description of the kernel INSTANCE the last GEMM-family call of this
+ * thread dispatched to (e.g. "gemm_tn kind=0 bn=256 stages=4 mc=1 splits=1 out=bf16 grid=148",
+ * "fp8_block_gemm bn=256 tiles=768", "w4a16_gemm bm=256 swap=0 splits=1 tiles=...") so that parity
+ * tests can assert that a shape reached the instance it is meant to cover. */
+const char* b200_last_variant(void);
 /* Number of kernels this library has launched so far in this process
  * (bench.py's gpu_launches counter). */
 int64_t b200_launch_count(void);

@@ -32,7 +32,10 @@ def static_quant_fp8_oracle(x: torch.Tensor, scale: torch.Tensor):
 
 def per_token_group_quant_fp8_oracle(x: torch.Tensor, group_size: int = 128, eps: float = 1e-10):
     """Per-(token, group) quantisation, true division by the scale
-    (native_per_token_group_quant_fp8, python/sglang/test/test_block_fp8.py:23-48)."""
+    (native_per_token_group_quant_fp8, python/sglang/test/test_block_fp8.py:23-48).  The eps clamp is
+    applied to the fp32 absmax as the reference's kernels do (fp8_kernel.py:133,
+    per_token_group_quant_8bit.cu:40); the in-test twin clamps in the input dtype, which only
+    differs for all-zero groups (tests/test_oracle_pinned.py spells that out)."""
     assert x.shape[-1] % group_size == 0
     g = x.float().reshape(-1, group_size)
     amax = g.abs().amax(dim=-1, keepdim=True).clamp(min=eps)
@@ -62,7 +65,7 @@ def block_scaled_mm_oracle(a, b, a_s, b_s, block_size=(128, 128), out_dtype=torc
     af, bf = a.float(), b.float()
     m, k = af.shape
     n = bf.shape[0]
-    c = torch.zeros((m, n), dtype=torch.float32)
+    c = torch.zeros((m, n), dtype=torch.float32, device=af.device)
     for kb in range((k + bk - 1) // bk):
         ks = slice(kb * bk, min((kb + 1) * bk, k))
         for nb in range((n + bn - 1) // bn):

@@ -18,7 +18,7 @@ AWQ_ORDER = [0, 4, 1, 5, 2, 6, 3, 7]  # output column j of a word sits at nibble
 
 def unpack_awq_int4(packed: torch.Tensor) -> torch.Tensor:
     """[R, C] int32 -> [R, 8C] integers 0..15 in output-column order (bit-exact target)."""
-    shifts = torch.tensor([4 * o for o in AWQ_ORDER], dtype=torch.int32)
+    shifts = torch.tensor([4 * o for o in AWQ_ORDER], dtype=torch.int32, device=packed.device)
     nib = (packed.unsqueeze(-1) >> shifts) & 0xF
     return nib.reshape(packed.shape[0], -1)
 

@@ -19,6 +19,7 @@ BF16, F16, F32, FP8_E4M3 = 0, 1, 2, 3
 _SIGNATURES = {
     "b200_version": (c_int, []),
     "b200_last_error": (c_char_p, []),
+    "b200_last_variant": (c_char_p, []),
     "b200_launch_count": (c_int64, []),
     "b200_set_pdl": (c_int, [c_int]),
     "b200_timing_enable": (c_int, [c_int]),
@@ -152,6 +153,12 @@ def check(status: int, what: str) -> None:
     if status != 0:
         msg = load().b200_last_error()
         raise B200Error(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def last_variant() -> str:
+    """Which kernel instance the last GEMM-family call of this thread dispatched to (test hook)."""
+    v = load().b200_last_variant()
+    return v.decode() if v else ""
 
 
 def set_pdl(on) -> int:

@@ -49,6 +49,11 @@ extern std::atomic<int64_t> g_launch_count;
     }                                                                                 \
   } while (0)
 
+// Debug / test hook: every dispatcher records WHICH kernel instance it launched last on this host
+// thread (tile shape, split factor, multicast, ...) so that parity tests can assert that a shape
+// really reached the instance it is meant to cover (b200_last_variant()).
+void note_variant(const char* fmt, ...);
+
 // Optional per-kernel device timing (bench.py's roofline leg): when enabled through
 // b200_timing_enable(1), every launch wrapped in a ScopedKernelTimer is bracketed by CUDA events
 // on the launching stream; b200_timing_read() accumulates the elapsed times per kernel name.

@@ -238,6 +238,7 @@ static int launch_block_gemm_bn(const void* a, int64_t lda, const void* b, int64
   }
   const int tiles = ceil_div(p.M, 128) * ceil_div(p.N, BN);
   const int sms = device_sm_count();
+  note_variant("fp8_block_gemm bn=%d tiles=%d", BN, tiles);
   {
     ScopedKernelTimer timer("fp8_block_gemm", st);
     B200_CUDA_OK(launch_kernel(kern, dim3(tiles < sms ? tiles : sms), dim3(kBlkThreads), SMEM, st, 1, pdl_family(p.M, kPdlGemmBig), ta, tb, p));

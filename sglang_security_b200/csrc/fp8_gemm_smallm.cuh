@@ -412,6 +412,8 @@ int launch_smallm_ks(const void* x, int64_t ldx, const void* w, int64_t ldw, Sma
   if (S > num_kb) S = num_kb;
   p.kb_per_split = ceil_div(num_kb, S);
   p.pdl_late = pdl_late();
+  note_variant("fp8_smallm mt=%d blk=%d ar=%d ksub=%d splits=%d tiles=%d", MT, BLK ? 1 : 0,
+               AR ? 1 : 0, KSUB, S, n_tiles);
   {
     ScopedKernelTimer timer(timer_name, st);
     B200_CUDA_OK(launch_kernel(kern, dim3(n_tiles * S), dim3(192), C::SMEM_BYTES, st, S, pdl_family(p.M, kPdlGemmSmall), tw, tx, p));

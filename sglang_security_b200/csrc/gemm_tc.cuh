@@ -10,6 +10,7 @@
 // static persistent tile schedule (tile = blockIdx.x + i * gridDim.x, M fastest so concurrently
 // running CTAs share the same weight tile through L2).
 #pragma once
+#include <type_traits>
 
 #include "tc_common.cuh"
 
@@ -463,6 +464,9 @@ int launch_gemm_tn(const void* a, int64_t lda, const void* b, int64_t ldb,
     const int pairs = (ceil_div(ep.M, C::BLOCK_M) / 2) * ceil_div(ep.N, BLOCK_N);
     grid = 2 * (pairs < sms / 2 ? pairs : sms / 2);
   }
+  note_variant("gemm_tn kind=%d bn=%d stages=%d mc=%d splits=%d out=%s grid=%d", KIND, BLOCK_N, STAGES,
+               MC ? 1 : 0, ep.splits, sizeof(OutT) == 2 && std::is_same<OutT, __half>::value ? "f16" : "bf16",
+               grid);
   {
     ScopedKernelTimer timer(timer_name, st);
     B200_CUDA_OK(launch_kernel(kern, dim3(grid), dim3(C::THREADS), C::SMEM_BYTES, st, MC ? 2 : ep.splits, pdl_family(ep.M, kPdlGemmBig), ta, tb, ep));

@@ -35,6 +35,15 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static thread_local char g_variant[256] = "";
+void note_variant(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_variant, sizeof(g_variant), fmt, ap);
+  va_end(ap);
+}
+const char* last_variant() { return g_variant; }
+
 int device_sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -124,6 +133,8 @@ int b200_set_pdl(int on) {
 }
 
 const char* b200_last_error(void) { return b200::g_error; }
+
+const char* b200_last_variant(void) { return b200::last_variant(); }
 
 int64_t b200_launch_count(void) { return b200::g_launch_count.load(); }
 

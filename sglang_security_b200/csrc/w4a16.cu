@@ -749,6 +749,7 @@ static int launch_w4a16_gemm(const void* x, int64_t ldx, W4GemmParams p, cudaStr
     while (S > 1 && (S - 1) * ceil_div(num_kb, S) >= num_kb) --S;
     p.kb_per_split = ceil_div(num_kb, S);
   }
+  note_variant("w4a16_gemm bm=%d swap=%d splits=%d tiles=%d", BM, SWAP ? 1 : 0, S, tiles);
   {
     ScopedKernelTimer timer("w4a16_gemm", st);
     if (S > 1) {

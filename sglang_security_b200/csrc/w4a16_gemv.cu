@@ -415,6 +415,7 @@ int b200_w4a16_gemv(const void* x, int64_t ldx, const void* qweight, const void*
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kGvSmem));
     attr_done[ai] = true;
   }
+  note_variant("w4a16_gemv splits=%d tiles=%d", S, n_tiles);
   {
     ScopedKernelTimer timer("w4a16_gemv", st);
     B200_CUDA_OK(launch_kernel(kern, dim3(n_tiles * S), dim3(kGvThreads), kGvSmem, st, S,

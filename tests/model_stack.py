@@ -37,12 +37,22 @@ class StackConfig:
     quant: Optional[str] = None    # None | "fp8" | "fp8_block"
 
 
-def init_weights(cfg: StackConfig, seed: int = 0, std: float = 0.02):
+def init_weights(cfg: StackConfig, seed: int = 0, std: float = 0.02, decisive_embed_std: float = 0.0):
+    """N(0, std) weights.  With `decisive_embed_std` > 0 the head is TIED to the embedding through a
+    fixed random permutation (lm_head[v] = embed[perm[v]]; Qwen2.5-0.5B ties its head, HF config
+    tie_word_embeddings) and the embedding gets that std, so the residual stream carries a token
+    signal as large as the 24 layers' contributions: the greedy token then wins by a margin far
+    above the bf16 / fp8 numeric noise instead of being a near-tie among 32000 random logits
+    (SURVEY §8d cfg 1: random-init logits are nearly tied, report the margin)."""
     g = torch.Generator().manual_seed(seed)
     r = lambda *s: (torch.randn(*s, generator=g) * std).to(torch.bfloat16)
     qkv_out = (cfg.heads + 2 * cfg.kv_heads) * cfg.head_dim
     w = {"embed": r(cfg.vocab, cfg.hidden), "lm_head": r(cfg.vocab, cfg.hidden),
          "final_norm": torch.ones(cfg.hidden, dtype=torch.bfloat16), "layers": []}
+    if decisive_embed_std > 0:
+        w["embed"] = (torch.randn(cfg.vocab, cfg.hidden, generator=g) * decisive_embed_std).to(
+            torch.bfloat16)
+        w["lm_head"] = w["embed"][torch.randperm(cfg.vocab, generator=g)].contiguous()
     for _ in range(cfg.layers):
         w["layers"].append(dict(
             in_norm=(1 + 0.1 * torch.randn(cfg.hidden, generator=g)).to(torch.bfloat16),

@@ -100,3 +100,60 @@ def test_fused_layer_equals_unfused_layer_bit_exact(quant):
     for l in range(cfg.layers):
         assert torch.equal(outs[0][2].kvp.k_buffer[l], outs[1][2].kvp.k_buffer[l])
         assert torch.equal(outs[0][2].kvp.v_buffer[l], outs[1][2].kvp.v_buffer[l])
+
+
+def _free_running(cfg, embed_std, decode_steps, bs, prefix, own, noise_budget):
+    """Both stacks decode FREE-RUNNING (each feeds back its own argmax).  The init gives every greedy
+    decision a margin far above the numeric noise (model_stack.init_weights, decisive_embed_std), so
+    the token streams must be IDENTICAL; the margin / noise ratio is measured and asserted."""
+    weights = MS.init_weights(cfg, seed=0, std=0.02, decisive_embed_std=embed_std)
+    g = torch.Generator().manual_seed(1)
+    prefix_ids = torch.randint(0, cfg.vocab, (prefix,), generator=g)
+    suffix = [torch.randint(0, cfg.vocab, (own,), generator=g) for _ in range(bs)]
+    kw = dict(pool_size=prefix + bs * (own + decode_steps) + 8, max_reqs=bs + 1,
+              max_ctx=prefix + own + decode_steps + 4)
+    ref = MS.Stack(cfg, weights, "oracle", **kw)
+    tok_ref, logits_ref = MS.run_shared_prefix_session(ref, prefix_ids, suffix, decode_steps)
+    gpu = MS.Stack(cfg, weights, "b200", **kw)
+    tok_gpu, logits_gpu = MS.run_shared_prefix_session(gpu, prefix_ids, suffix, decode_steps)
+    min_margin, worst = float("inf"), 0.0
+    for lr, lg in zip(logits_ref, logits_gpu):
+        top = lr.topk(2, dim=-1).values
+        min_margin = min(min_margin, (top[:, 0] - top[:, 1]).min().item())
+        worst = max(worst, (lr - lg).abs().max().item())
+    sigma = logits_ref[0].std().item()
+    print(f"[e2e free-running] {tok_ref.numel()} tokens, min top-1 margin {min_margin:.1f}, worst "
+          f"logit diff {worst:.2f} (logit std {sigma:.1f}) -> margin/noise {min_margin / max(worst, 1e-9):.1f}")
+    assert torch.equal(tok_ref, tok_gpu), (tok_ref != tok_gpu).sum().item()
+    assert worst <= noise_budget * sigma, (worst, sigma)
+    assert min_margin >= 4 * worst, (min_margin, worst)
+    # the stream is not degenerate: requests produce different, changing tokens
+    assert tok_ref.unique().numel() >= tok_ref.numel() // 2
+    assert torch.equal(gpu.rtp.req_to_token.cpu(), ref.rtp.req_to_token)
+    return ref, gpu
+
+
+def test_greedy_free_running_identical_bf16_cfg1():
+    """BASELINE cfg 1 at full geometry (Qwen2.5-0.5B: 24 layers, hidden 896, 14/2 heads, D 64, qkv
+    bias, tied head), 512-token shared radix prefix, 8 requests x 16 own tokens, 32 greedy decode
+    steps: 264 greedy tokens, zero mismatches."""
+    cfg = MS.StackConfig()
+    ref, gpu = _free_running(cfg, 1.0, decode_steps=32, bs=8, prefix=512, own=16, noise_budget=0.15)
+    used = ref.next_slot
+    for l in (0, cfg.layers - 1):
+        dk = (gpu.kvp.k_buffer[l][:used].float().cpu() - ref.kvp.k_buffer[l][:used].float()).abs().max()
+        assert dk.item() <= 0.5, (l, dk)
+
+
+def test_greedy_free_running_identical_fp8_small():
+    cfg = MS.StackConfig(hidden=1024, heads=8, kv_heads=2, head_dim=128, inter=2816, layers=4,
+                         vocab=8192, qkv_bias=False, quant="fp8")
+    _free_running(cfg, 1.0, decode_steps=16, bs=4, prefix=200, own=9, noise_budget=0.5)
+
+
+def test_greedy_free_running_identical_fp8_llama8b_width():
+    """FP8 W8A8 linear layers at the full Llama-3.1-8B layer width (hidden 4096, 32/8 heads, D 128,
+    intermediate 14336), 2 layers."""
+    cfg = MS.StackConfig(hidden=4096, heads=32, kv_heads=8, head_dim=128, inter=14336, layers=2,
+                         vocab=16384, rope_theta=5e5, eps=1e-5, qkv_bias=False, quant="fp8")
+    _free_running(cfg, 1.0, decode_steps=8, bs=4, prefix=128, own=8, noise_budget=0.5)

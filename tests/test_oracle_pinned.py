@@ -1,0 +1,67 @@
+"""CPU: the oracle restatements of the quantised-linear ops against fixtures produced by the
+reference's OWN in-test torch functions (oracle/gen_golden_quant.py extracts their source unmodified
+from /root/reference and runs it).  This is what pins oracle/fp8.py and oracle/int4.py (AWQ)."""
+import os
+
+import torch
+
+from oracle import fp8 as OF
+from oracle import int4 as OI
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _load(name):
+    return torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
+
+
+def zero_group_mask(x, group):
+    return x.float().reshape(x.shape[0], -1, group).abs().amax(-1) == 0
+
+
+def test_awq_dequant_oracle_equals_reference_function():
+    for c in _load("awq_dequant"):
+        out = OI.awq_dequantize_oracle(c["qweight"], c["scales"], c["qzeros"], c["group"])
+        assert out.dtype == c["out"].dtype
+        assert torch.equal(out.view(torch.int16), c["out"].view(torch.int16))
+        # the integer unpack itself (bit-exact target of north_star)
+        w = OI.unpack_awq_int4(c["qweight"])
+        assert w.min() >= 0 and w.max() <= 15
+
+
+def test_fp8_quantisers_oracle_equals_reference_functions():
+    for c in _load("fp8_quant"):
+        q, s = OF.per_token_quant_fp8_oracle(c["x"])
+        assert torch.equal(s.reshape(-1), c["token_scale"])
+        keep = torch.ones(c["x"].shape[0], dtype=torch.bool)
+        keep[c["zero_rows"]] = False      # scale 0: the reference twin divides by it
+        assert torch.equal(q[keep].view(torch.uint8), c["q_token"][keep].view(torch.uint8))
+        assert (q[~keep].float() == 0).all()
+        qg, sg = OF.per_token_group_quant_fp8_oracle(c["x_group"], 128)
+        live = zero_group_mask(c["x_group"], 128).logical_not()
+        assert torch.equal(sg[live], c["s_group"][live])
+        live_q = live.repeat_interleave(128, dim=1)
+        assert torch.equal(qg.view(torch.uint8)[live_q], c["q_group"].view(torch.uint8)[live_q])
+        # all-zero groups: the reference's KERNELS clamp the fp32 absmax with eps
+        # (fp8_kernel.py:133 `tl.maximum(tl.max(tl.abs(y)), eps)`, per_token_group_quant_8bit.cu:40
+        # `local_absmax = eps`), its in-test torch twin clamps in the INPUT dtype (bf16 rounds
+        # 1e-10, fp16 flushes it to 0 and then divides 0/0); the oracle follows the kernels
+        assert (sg[~live] == torch.tensor(1e-10, dtype=torch.float32) / 448.0).all()
+        assert (qg.float()[~live_q] == 0).all()
+        qs = OF.static_quant_fp8_oracle(c["x"], c["static_scale"])
+        assert torch.equal(qs.view(torch.uint8), c["q_static"].view(torch.uint8))
+
+
+def test_fp8_scaled_mm_oracle_equals_reference_function():
+    for c in _load("fp8_gemm"):
+        out = OF.scaled_mm_oracle(c["a"], c["b"].t(), c["scale_a"], c["scale_b"], c["out"].dtype,
+                                  c["bias"])
+        assert torch.equal(out, c["out"])
+
+
+def test_fp8_block_mm_oracle_equals_reference_function():
+    for c in _load("fp8_block"):
+        out = OF.block_scaled_mm_oracle(c["a"], c["b"], c["a_s"], c["b_s"], (128, 128),
+                                        c["out"].dtype)
+        # same tile order and fp32 accumulation as native_w8a8_block_fp8_matmul
+        assert torch.equal(out, c["out"])

@@ -1,0 +1,71 @@
+"""GPU: the CUDA kernels (through the C-ABI) against fixtures produced by the reference's OWN in-test
+torch functions (oracle/gen_golden_quant.py).  Integer / byte results bit-exact; GEMMs within the
+reference tests' tolerances (test_fp8_gemm.py:33-35 rtol 0.02 / atol 1; test_block_fp8.py:392-396
+relative mean error < 1e-3) and the tighter bound of one output rounding."""
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+FP8 = torch.float8_e4m3fn
+
+
+def _load(name):
+    return torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
+
+
+def test_awq_dequant_kernel_equals_reference_function():
+    from sglang_security_b200.layers.quantization.w4a16_kernel import awq_dequantize
+
+    for c in _load("awq_dequant"):
+        out = awq_dequantize(c["qweight"].cuda(), c["scales"].cuda(), c["qzeros"].cuda())
+        assert torch.equal(out.cpu().view(torch.int16), c["out"].view(torch.int16))
+
+
+def test_fp8_quant_kernels_equal_reference_functions():
+    from sglang_security_b200.layers.quantization.fp8_kernel import (per_token_group_quant_fp8,
+                                                                    sglang_per_token_quant_fp8,
+                                                                    static_quant_fp8)
+
+    for c in _load("fp8_quant"):
+        q, s = sglang_per_token_quant_fp8(c["x"].cuda())
+        assert torch.equal(s.cpu().reshape(-1), c["token_scale"])
+        keep = torch.ones(c["x"].shape[0], dtype=torch.bool)
+        keep[c["zero_rows"]] = False
+        assert torch.equal(q.cpu()[keep].view(torch.uint8), c["q_token"][keep].view(torch.uint8))
+        assert (q.cpu()[~keep].float() == 0).all()
+        qg, sg = per_token_group_quant_fp8(c["x_group"].cuda(), 128)
+        live = c["x_group"].float().reshape(c["x"].shape[0], -1, 128).abs().amax(-1) != 0
+        assert torch.equal(sg.cpu()[live], c["s_group"][live])
+        live_q = live.repeat_interleave(128, dim=1)
+        assert torch.equal(qg.cpu().view(torch.uint8)[live_q], c["q_group"].view(torch.uint8)[live_q])
+        # all-zero groups follow the reference KERNELS' fp32 eps clamp (see test_oracle_pinned.py)
+        assert (sg.cpu()[~live] == torch.tensor(1e-10) / 448.0).all()
+        qs, _ = static_quant_fp8(c["x"].cuda(), c["static_scale"].cuda())
+        assert torch.equal(qs.cpu().view(torch.uint8), c["q_static"].view(torch.uint8))
+
+
+def test_fp8_scaled_mm_kernel_vs_reference_function():
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_scaled_mm
+
+    for c in _load("fp8_gemm"):
+        ref = c["out"]
+        bias = None if c["bias"] is None else c["bias"].cuda()
+        out = fp8_scaled_mm(c["a"].cuda(), c["b"].cuda().t(), c["scale_a"].cuda(),
+                            c["scale_b"].cuda(), ref.dtype, bias)
+        torch.testing.assert_close(out.cpu(), ref, rtol=0.02, atol=1)
+        err = (out.cpu().float() - ref.float()).abs().max().item()
+        assert err <= 2e-2 * max(1.0, ref.float().abs().max().item()), err
+
+
+def test_fp8_block_mm_kernel_vs_reference_function():
+    from sglang_security_b200.layers.quantization.fp8_kernel import fp8_blockwise_scaled_mm
+
+    for c in _load("fp8_block"):
+        ref = c["out"]
+        out = fp8_blockwise_scaled_mm(c["a"].cuda(), c["b"].cuda(), c["a_s"].cuda(),
+                                      c["b_s"].cuda(), ref.dtype)
+        rel = (out.cpu().float() - ref.float()).abs().mean() / ref.float().abs().mean()
+        assert rel.item() < 1e-3, rel.item()
