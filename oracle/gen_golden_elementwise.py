@@ -46,6 +46,16 @@ def cases():
         out[name] = dict(positions=pos, q=q, k=k, q_out=qo, k_out=ko,
                          cos_sin_cache=rope.cos_sin_cache.clone(), head_size=d, rotary_dim=rot,
                          is_neox=neox, base=10000, max_pos=512)
+    # Llama-3.1 rope_scaling (config.json of Llama-3.1-8B/70B): cos/sin table of the reference's
+    # get_rope(..., rope_scaling={'rope_type': 'llama3', ...}) -> Llama3RotaryEmbedding
+    rope_mod = ref_loader.load_rope_module()
+    scaling = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
+               "high_freq_factor": 4.0, "original_max_position_embeddings": 8192}
+    rope_mod._ROPE_DICT.clear()
+    r3 = rope_mod.get_rope(128, 128, 2048, 500000.0, True, dict(scaling), torch.bfloat16)
+    assert type(r3).__name__ == "Llama3RotaryEmbedding", type(r3)
+    out["rope_llama3_d128"] = dict(cos_sin_cache=r3.cos_sin_cache.clone(), head_size=128,
+                                   rotary_dim=128, max_pos=2048, base=500000.0, rope_scaling=scaling)
     return out
 
 

@@ -141,4 +141,15 @@ def load_elementwise_layers():
         else:
             sys.modules.pop("sgl_kernel", None)
     _elementwise = (ln.RMSNorm, act.SiluAndMul, rope.RotaryEmbedding)
+    global _rope_module
+    _rope_module = rope
     return _elementwise
+
+
+_rope_module = None
+
+
+def load_rope_module():
+    """The UNMODIFIED reference layers/rotary_embedding.py module (get_rope, Llama3RotaryEmbedding)."""
+    load_elementwise_layers()
+    return _rope_module

@@ -96,6 +96,65 @@ class ColumnParallelLinear(LinearBase):
         assert param.shape == loaded_weight.shape, (param.shape, loaded_weight.shape)
         param.data.copy_(loaded_weight)
 
+    # ---- fused layers (gate_up, qkv): the reference's `loaded_shard_id` contract ----------------
+    def _load_logical_shard(self, param: Parameter, loaded_weight: torch.Tensor, slot: int,
+                            offset: int, size: int, rank_index: int):
+        """Copy one logical projection of a fused parameter.  `offset`/`size` are this rank's
+        window in UNPACKED output rows (linear.py:615-640 / 1060-1110); `rank_index` selects the
+        slice of the checkpoint tensor (tp_rank, or tp_rank // replicas for replicated kv heads).
+        int4-packed and block-scale parameters rescale the window
+        (parameter.py:340-375 `adjust_shard_indexes_for_packing`, linear.py:731-741)."""
+        output_dim = getattr(param, "output_dim", None)
+        if output_dim is None:
+            # one scalar per logical shard (Fp8 per-tensor scales, linear.py:78-94
+            # `adjust_scalar_to_fused_array`): slot = logical shard index
+            if loaded_weight.numel() != 1:
+                raise ValueError(f"fused parameter without output_dim expects a scalar per shard, "
+                                 f"got {tuple(loaded_weight.shape)}")
+            param.data[slot].copy_(loaded_weight.reshape(()))
+            return
+        if getattr(param, "packed_dim", None) == output_dim:
+            factor = param.packed_factor
+            if offset % factor or size % factor:
+                raise ValueError(f"shard window ({offset}, {size}) is not a multiple of the pack "
+                                 f"factor {factor}")
+            offset, size = offset // factor, size // factor
+        block_n = getattr(param, "block_n", None)
+        if block_n is not None:  # [N/block_n, K/block_k] scale grid
+            offset, size = (offset + block_n - 1) // block_n, (size + block_n - 1) // block_n
+        window = param.data.narrow(output_dim, offset, size)
+        if loaded_weight.shape[output_dim] != size:
+            if loaded_weight.shape[output_dim] < (rank_index + 1) * size:
+                raise ValueError(f"checkpoint shard of width {loaded_weight.shape[output_dim]} has no "
+                                 f"window {rank_index} of size {size}")
+            loaded_weight = loaded_weight.narrow(output_dim, rank_index * size, size)
+        if window.shape != loaded_weight.shape:
+            raise ValueError(f"shard shape {tuple(loaded_weight.shape)} does not fit the "
+                             f"parameter window {tuple(window.shape)}")
+        window.copy_(loaded_weight)
+
+    def _split_fused_checkpoint(self, param: Parameter, loaded_weight: torch.Tensor, ids, sizes):
+        """A tensor already fused on disk (Phi-3 style, linear.py:560-606, 983-1040): cut it into
+        its logical projections (FULL, un-sharded widths) and load each with its shard id."""
+        output_dim = getattr(param, "output_dim", None)
+        if output_dim is None:
+            if loaded_weight.numel() == 1:      # one per-tensor scale for the fused tensor
+                param.data.fill_(loaded_weight.reshape(()).item())
+            else:
+                assert param.shape == loaded_weight.shape, (param.shape, loaded_weight.shape)
+                param.data.copy_(loaded_weight)
+            return
+        start = 0
+        for sid, full in zip(ids, sizes):
+            lo, width = start, full
+            if getattr(param, "packed_dim", None) == output_dim:
+                lo, width = lo // param.packed_factor, width // param.packed_factor
+            block_n = getattr(param, "block_n", None)
+            if block_n is not None:
+                lo, width = (lo + block_n - 1) // block_n, (width + block_n - 1) // block_n
+            self.weight_loader(param, loaded_weight.narrow(output_dim, lo, width), sid)
+            start += full
+
     def forward(self, input_):
         bias = self.bias if not self.skip_bias_add else None
         output = self.quant_method.apply(self, input_, bias)
@@ -110,6 +169,20 @@ class MergedColumnParallelLinear(ColumnParallelLinear):
     def __init__(self, input_size: int, output_sizes: List[int], bias: bool = True, **kw):
         self.output_sizes = output_sizes
         super().__init__(input_size, sum(output_sizes), bias=bias, output_sizes=output_sizes, **kw)
+
+    def weight_loader(self, param: Parameter, loaded_weight: torch.Tensor,
+                      loaded_shard_id: Optional[int] = None):
+        """linear.py:523-660: `loaded_shard_id` = index of the logical projection (0 = gate,
+        1 = up); None = the checkpoint tensor is already fused."""
+        if loaded_shard_id is None:
+            self._split_fused_checkpoint(param, loaded_weight, range(len(self.output_sizes)),
+                                         self.output_sizes)
+            return
+        if not 0 <= loaded_shard_id < len(self.output_sizes):
+            raise ValueError(f"loaded_shard_id {loaded_shard_id} out of range")
+        offset = sum(self.output_sizes[:loaded_shard_id]) // self.tp_size
+        size = self.output_sizes[loaded_shard_id] // self.tp_size
+        self._load_logical_shard(param, loaded_weight, loaded_shard_id, offset, size, self.tp_rank)
 
 
 class QKVParallelLinear(ColumnParallelLinear):
@@ -131,6 +204,28 @@ class QKVParallelLinear(ColumnParallelLinear):
         sizes = [self.num_heads * head_size * tp_size, self.num_kv_heads * head_size * tp_size,
                  self.num_kv_heads * head_size * tp_size]
         super().__init__(hidden_size, out, bias=bias, output_sizes=sizes, **kw)
+
+    _SLOT = {"q": 0, "k": 1, "v": 2}
+
+    def weight_loader(self, param: Parameter, loaded_weight: torch.Tensor,
+                      loaded_shard_id: Optional[str] = None):
+        """linear.py:937-1128: `loaded_shard_id` in {"q", "k", "v"}; kv heads replicated over
+        `num_kv_head_replicas` ranks read the same checkpoint slice (tp_rank // replicas)."""
+        hd = self.head_size
+        if loaded_shard_id is None:
+            self._split_fused_checkpoint(
+                param, loaded_weight, ("q", "k", "v"),
+                (self.total_num_heads * hd, self.total_num_kv_heads * hd,
+                 self.total_num_kv_heads * hd))
+            return
+        if loaded_shard_id not in self._SLOT:
+            raise ValueError(f"loaded_shard_id must be 'q', 'k' or 'v', got {loaded_shard_id!r}")
+        q, kv = self.num_heads * hd, self.num_kv_heads * hd
+        offset, size = {"q": (0, q), "k": (q, kv), "v": (q + kv, kv)}[loaded_shard_id]
+        rank_index = (self.tp_rank if loaded_shard_id == "q"
+                      else self.tp_rank // self.num_kv_head_replicas)
+        self._load_logical_shard(param, loaded_weight, self._SLOT[loaded_shard_id], offset, size,
+                                 rank_index)
 
 
 class RowParallelLinear(LinearBase):

@@ -99,7 +99,9 @@ class Fp8LinearMethod(LinearMethodBase):
         if self.block_quant:
             scale = Parameter(torch.full(((n + block_n - 1) // block_n, (k + block_k - 1) // block_k),
                                          fmin, dtype=torch.float32), requires_grad=False)
-            set_weight_attrs(scale, {"input_dim": 1, "output_dim": 0, "weight_loader": weight_loader})
+            # block_n: fused-shard loaders convert row windows to scale-grid rows (linear.py:731-741)
+            set_weight_attrs(scale, {"input_dim": 1, "output_dim": 0, "block_n": block_n,
+                                     "weight_loader": weight_loader})
             layer.register_parameter("weight_scale_inv", scale)
         else:
             scale = Parameter(torch.full((len(output_partition_sizes),), fmin, dtype=torch.float32),

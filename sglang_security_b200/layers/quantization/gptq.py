@@ -73,6 +73,13 @@ class GPTQLinearMethod(LinearMethodBase):
         if n % cfg.pack_factor != 0:
             raise ValueError("The output size is not aligned with the quantized weight shape. "
                              "This can be caused by too large tensor parallel size.")
+        if cfg.desc_act and input_size_per_partition != input_size:
+            # act-order rows of one K shard belong to arbitrary GLOBAL groups: the reference's
+            # dependency (vllm GPTQLinearMethod.create_weights) then loads scales / zeros
+            # unsharded and indexes them through g_idx.  The B200 kernel needs group-contiguous
+            # rows per rank, which such a shard cannot provide -> fail loudly, not silently wrong.
+            raise NotImplementedError("GPTQ desc_act=True on a row-parallel layer with tp_size > 1 "
+                                      "is not supported by the B200 W4A16 kernel")
         weight_loader = extra_weight_attrs.get("weight_loader")
         k = input_size_per_partition
         qweight = Parameter(torch.empty(k // cfg.pack_factor, n, dtype=torch.int32), requires_grad=False)
@@ -96,7 +103,10 @@ class GPTQLinearMethod(LinearMethodBase):
         k = layer.qweight.shape[0] * self.quant_config.pack_factor
         group = layer.w4a16_group_size
         g_idx = layer.g_idx.data.to(torch.int64)
-        trivial = bool(torch.equal(g_idx, torch.arange(k, device=g_idx.device) // group))
+        # desc_act=False: checkpoints still store g_idx (AutoGPTQ writes arange(K)//group with
+        # GLOBAL group ids, so a K shard of rank > 0 never equals the local arange) -> ignore it.
+        trivial = (not self.quant_config.desc_act) or bool(
+            torch.equal(g_idx, torch.arange(k, device=g_idx.device) // group))
         perm = None
         if not trivial:
             # desc_act: make every group's rows contiguous, remember how to gather x columns

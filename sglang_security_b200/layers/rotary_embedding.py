@@ -8,6 +8,7 @@ rotated key and the value into the same kernel (b200_rope_kv_write); a model tha
 attention layer with save_kv_cache=False."""
 from __future__ import annotations
 
+import math
 from typing import Optional, Tuple
 
 import torch
@@ -117,7 +118,51 @@ class RotaryEmbedding(nn.Module):
         return query, key
 
 
+class Llama3RotaryEmbedding(RotaryEmbedding):
+    """Llama-3.1 frequency rescale (rotary_embedding.py:706-750): wavelengths shorter than
+    orig_max/high_freq_factor keep their frequency, longer than orig_max/low_freq_factor are divided
+    by `scaling_factor`, the band between is interpolated.  Only the cos/sin table changes; the
+    kernels are the same."""
+
+    def __init__(self, head_size: int, rotary_dim: int, max_position_embeddings: int, base: float,
+                 is_neox_style: bool, dtype: torch.dtype, scaling_factor: float,
+                 low_freq_factor: float, high_freq_factor: float, orig_max_position: int,
+                 native_rounding: bool = False) -> None:
+        self.scaling_factor = scaling_factor
+        self.low_freq_factor = low_freq_factor
+        self.high_freq_factor = high_freq_factor
+        self.orig_max_position = orig_max_position
+        super().__init__(head_size, rotary_dim, max_position_embeddings, base, is_neox_style, dtype,
+                         native_rounding)
+
+    def _compute_inv_freq(self, base: float) -> torch.Tensor:
+        inv_freq = super()._compute_inv_freq(base)
+        wave_len = 2 * math.pi / inv_freq
+        lo_len = self.orig_max_position / self.low_freq_factor
+        hi_len = self.orig_max_position / self.high_freq_factor
+        smooth = 0
+        if self.low_freq_factor != self.high_freq_factor:
+            smooth = ((self.orig_max_position / wave_len - self.low_freq_factor)
+                      / (self.high_freq_factor - self.low_freq_factor))
+        scaled = inv_freq / self.scaling_factor
+        mid = (1 - smooth) * scaled + smooth * inv_freq
+        return torch.where(wave_len < hi_len, inv_freq, torch.where(wave_len > lo_len, scaled, mid))
+
+
 def get_rope(head_size: int, rotary_dim: int, max_position: int, base: float,
-             is_neox_style: bool = True, dtype: torch.dtype = torch.bfloat16) -> RotaryEmbedding:
-    """Subset of the reference factory (rotary_embedding.py get_rope): plain (unscaled) RoPE."""
-    return RotaryEmbedding(head_size, rotary_dim, max_position, base, is_neox_style, dtype)
+             is_neox_style: bool = True, rope_scaling: Optional[dict] = None,
+             dtype: torch.dtype = torch.bfloat16) -> RotaryEmbedding:
+    """Subset of the reference factory (rotary_embedding.py:1083-1300 get_rope): unscaled RoPE and
+    the `llama3` scaling the BASELINE models (Llama-3.1-8B / 70B) use.  Every other rope_scaling
+    type raises instead of silently building unscaled tables."""
+    if rope_scaling is None:
+        return RotaryEmbedding(head_size, rotary_dim, max_position, base, is_neox_style, dtype)
+    kind = rope_scaling.get("rope_type", rope_scaling.get("type"))
+    if kind == "default":
+        return RotaryEmbedding(head_size, rotary_dim, max_position, base, is_neox_style, dtype)
+    if kind == "llama3":
+        return Llama3RotaryEmbedding(head_size, rotary_dim, max_position, base, is_neox_style, dtype,
+                                     rope_scaling["factor"], rope_scaling["low_freq_factor"],
+                                     rope_scaling["high_freq_factor"],
+                                     rope_scaling["original_max_position_embeddings"])
+    raise NotImplementedError(f"rope_scaling type {kind!r} is not built (only None/'default'/'llama3')")
