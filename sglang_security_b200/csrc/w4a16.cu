@@ -576,6 +576,12 @@ w4a16_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
                        : "r"(zsrc + 256));
         }
       }
+      // The slot is refilled by TMA (async proxy) as soon as it is released, and the mbarrier release
+      // only orders this thread's generic-proxy accesses: without a proxy fence the refill may
+      // overtake the ld.shared above (write-after-read across proxies).  It showed whenever the
+      // MMA pipe, not the dequant warps, was the bottleneck (256-row tiles with K >= 3072, second
+      // tiles of persistent CTAs): a few stale weights per stage, different on every run.
+      tc::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(rempty_bar(rs));
       rs += DG;
