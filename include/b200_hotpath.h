@@ -257,6 +257,23 @@ int b200_w4a16_gemv(const void* x, int64_t ldx, const void* qweight, const void*
                     int K, int group_size, int dtype, void* stream);
 int b200_w4a16_gemv_config(int max_m, int splits);
 
+/* Decode-regime GEMV, second generation (csrc/w4a16_gemv2.cu): the same arithmetic as
+ * b200_w4a16_gemv on a one-time STREAM repack of the packed weight — tiles of 16 output columns x
+ * 64 k, 512 contiguous bytes, ordered [n / 16][k / 64], each lane's 16 bytes being its mma.sync A
+ * fragments — so that weights go HBM -> registers -> tensor core with no shared-memory staging.
+ *   b200_w4a16_gemv_v2_repack:    qweight [K, N/8] (AWQ nibble order, the layout b200_w4a16_gemm
+ *                                 takes) -> stream layout, K*N/2 bytes; K %% 64 == 0, N %% 16 == 0.
+ *   b200_w4a16_gemv_v2:           1 <= M <= 16; zeros / scales / bias / x / out as b200_w4a16_gemm.
+ *   b200_w4a16_gemv_v2_supported: 1 when the shape is accepted (group 32 or a multiple of 64).
+ *   b200_w4a16_gemv_v2_config:    splits > 0 fixes the split-K cluster size (tests / sweeps).
+ * Replaces awq_dequantize + torch.matmul (awq.py:203-215) / vllm ops.gptq_gemm for decode batches. */
+int b200_w4a16_gemv_v2_repack(const void* qweight, void* out, int K, int N, void* stream);
+int b200_w4a16_gemv_v2(const void* x, int64_t ldx, const void* qweight_stream, const void* zeros,
+                       const void* scales, const void* bias, void* out, int64_t ldc, int M, int N,
+                       int K, int group_size, int dtype, void* stream);
+int b200_w4a16_gemv_v2_supported(int M, int N, int K, int group_size);
+int b200_w4a16_gemv_v2_config(int splits);
+
 /* ---- steps either side of the GEMMs / attention ------------------ */
 /* (residual +) RMSNorm, optionally fused with the FP8 activation quantiser of the linear layer that
  * consumes it.  Replaces RMSNorm.forward (python/sglang/srt/layers/layernorm.py:61-108; oracle =

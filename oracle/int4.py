@@ -64,3 +64,22 @@ def w4a16_linear_oracle(x, w_dequant, bias=None):
     if bias is not None:
         out = out + bias
     return out.reshape(*x.shape[:-1], w_dequant.shape[1])
+
+
+def gemv_stream_layout_oracle(qweight: torch.Tensor) -> torch.Tensor:
+    """B200-internal stream layout of the decode GEMV (csrc/w4a16_gemv2.cu; no reference twin —
+    the reference never repacks AWQ weights): [K, N/8] packed words -> flat int32 words ordered
+    [n / 16][k / 64][lane = 4 g + t][j], word j = the 8 weights of column 16 nt + g + 8 (j & 1) at
+    k = 64 kb + 32 (j >> 1) + 8 t + {0, 2, 4, 6, 1, 3, 5, 7} (nibble order).  Pure index shuffling,
+    so the check is bit-exact."""
+    ints = unpack_awq_int4(qweight).to(torch.int64)            # [K, N]
+    k, n = ints.shape
+    assert k % 64 == 0 and n % 16 == 0
+    nt, kb, g, t, j, i = torch.meshgrid(torch.arange(n // 16), torch.arange(k // 64), torch.arange(8),
+                                        torch.arange(4), torch.arange(4), torch.arange(8),
+                                        indexing="ij")
+    col = nt * 16 + g + 8 * (j & 1)
+    kk = kb * 64 + (j >> 1) * 32 + 8 * t + torch.where(i < 4, 2 * i, 2 * (i - 4) + 1)
+    words = (ints[kk, col] << (4 * i)).sum(-1)                 # [nt, kb, g, t, j]
+    words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)
+    return words.reshape(-1).to(torch.int32)

@@ -95,6 +95,11 @@ _SIGNATURES = {
     "b200_w4a16_gemv": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv_config": (c_int, [c_int, c_int]),
+    "b200_w4a16_gemv_v2_repack": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "b200_w4a16_gemv_v2": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_w4a16_gemv_v2_supported": (c_int, [c_int, c_int, c_int, c_int]),
+    "b200_w4a16_gemv_v2_config": (c_int, [c_int]),
     "b200_rmsnorm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
                              c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_int, c_float,
                              c_int, c_float, c_int, c_void_p]),

@@ -10,7 +10,7 @@ import torch
 from torch.nn import Parameter
 
 from .base_config import LinearMethodBase, QuantizationConfig, set_weight_attrs
-from .w4a16_kernel import unpack_zeros, w4a16_gemm
+from .w4a16_kernel import gemv_stream_repack, stream_copy_enabled, unpack_zeros, w4a16_linear
 
 
 def is_layer_skipped_awq(prefix: str, modules_to_not_convert: List[str]) -> bool:
@@ -102,6 +102,10 @@ class AWQLinearMethod(LinearMethodBase):
         # one-time repack: packed zeros -> biased 16-bit zeros the fused kernel subtracts directly
         layer.b200_zeros = unpack_zeros(layer.qzeros.data, layer.scales.dtype, awq_order=True,
                                         add_one=False)
+        # decode batches stream a second, MMA-fragment-ordered copy of the same nibbles
+        # (+0.5 byte per weight; B200_W4A16_STREAM_COPY=0 keeps only the [K, N/8] layout)
+        layer.b200_qweight_stream = (gemv_stream_repack(layer.qweight.data)
+                                     if stream_copy_enabled() else None)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor,
               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -109,6 +113,5 @@ class AWQLinearMethod(LinearMethodBase):
         x2 = x.reshape(-1, x.shape[-1])
         if x2.stride(-1) != 1:
             x2 = x2.contiguous()
-        out = w4a16_gemm(x2, layer.qweight, layer.b200_zeros, layer.scales,
-                         layer.w4a16_group_size, bias)
+        out = w4a16_linear(x2, layer, bias)
         return out.reshape(out_shape)

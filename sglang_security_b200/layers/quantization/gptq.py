@@ -13,7 +13,8 @@ import torch
 from torch.nn import Parameter
 
 from .base_config import LinearMethodBase, QuantizationConfig, set_weight_attrs
-from .w4a16_kernel import repack_gptq, unpack_zeros, w4a16_gemm
+from .w4a16_kernel import (gemv_stream_repack, repack_gptq, stream_copy_enabled, unpack_zeros,
+                           w4a16_linear)
 
 
 class GPTQConfig(QuantizationConfig):
@@ -118,6 +119,10 @@ class GPTQLinearMethod(LinearMethodBase):
                                         add_one=True)
         layer.b200_perm = perm
         layer.scales = Parameter(layer.scales.data.contiguous(), requires_grad=False)
+        # decode batches stream a second, MMA-fragment-ordered copy of the same nibbles
+        # (+0.5 byte per weight; B200_W4A16_STREAM_COPY=0 keeps only the [K, N/8] layout)
+        layer.b200_qweight_stream = (gemv_stream_repack(layer.b200_qweight)
+                                     if stream_copy_enabled() else None)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor,
               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -127,6 +132,5 @@ class GPTQLinearMethod(LinearMethodBase):
             x2 = x2.index_select(-1, layer.b200_perm)
         elif x2.stride(-1) != 1:
             x2 = x2.contiguous()
-        out = w4a16_gemm(x2, layer.b200_qweight, layer.b200_zeros, layer.scales,
-                         layer.w4a16_group_size, bias)
+        out = w4a16_linear(x2, layer, bias)
         return out.reshape(out_shape)

@@ -1,6 +1,7 @@
 """INT4 weight-only kernels bound through the C-ABI (AWQ dequant, one-time repacks, fused GEMM)."""
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -71,6 +72,71 @@ def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, zeros: torch.Tensor, scal
                                      _lib.current_stream())
     _lib.check(rc, "b200_w4a16_gemm")
     return out
+
+
+def gemv_stream_repack(qweight: torch.Tensor) -> Optional[torch.Tensor]:
+    """One-time repack of the B200 [K, N/8] packed weight into the decode GEMV's stream layout
+    (csrc/w4a16_gemv2.cu): same bytes, ordered so that a warp's 512-byte load is its mma.sync A
+    fragments.  Returns None when the shape has no stream layout (K % 64 or N % 16 != 0)."""
+    _cuda(qweight, "gemv_stream_repack")
+    k, nc = qweight.shape
+    n = nc * 8
+    if k % 64 != 0 or n % 16 != 0:
+        return None
+    out = torch.empty(k * nc, device=qweight.device, dtype=torch.int32)
+    rc = _lib.load().b200_w4a16_gemv_v2_repack(qweight.contiguous().data_ptr(), out.data_ptr(), k, n,
+                                               _lib.current_stream())
+    _lib.check(rc, "b200_w4a16_gemv_v2_repack")
+    return out
+
+
+def gemv_v2_supported(m: int, n: int, k: int, group_size: int) -> bool:
+    return bool(_lib.load().b200_w4a16_gemv_v2_supported(int(m), int(n), int(k), int(group_size)))
+
+
+def w4a16_gemv_v2(x: torch.Tensor, qweight_stream: torch.Tensor, zeros: torch.Tensor,
+                  scales: torch.Tensor, group_size: int,
+                  bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x [M <= 16, K] @ dequant(stream-layout weight) (+ bias) -> [M, N]; N from the scales."""
+    _cuda(x, "w4a16_gemv_v2")
+    if x.dim() != 2 or x.stride(-1) != 1:
+        raise _lib.B200Error("w4a16_gemv_v2: x must be 2-D with contiguous rows")
+    m, k = x.shape
+    n = scales.shape[1]
+    if qweight_stream.numel() * 8 != k * n or scales.dtype != x.dtype or zeros.dtype != x.dtype:
+        raise _lib.B200Error("w4a16_gemv_v2: shape / dtype mismatch between x and the packed weight")
+    out = torch.empty((m, n), device=x.device, dtype=x.dtype)
+    if bias is not None and bias.dtype != x.dtype:
+        bias = bias.to(x.dtype)
+    rc = _lib.load().b200_w4a16_gemv_v2(x.data_ptr(), x.stride(0), qweight_stream.data_ptr(),
+                                        zeros.data_ptr(), scales.data_ptr(), _lib.ptr(bias),
+                                        out.data_ptr(), out.stride(0), m, n, k, group_size,
+                                        _lib.dtype_code(x.dtype), _lib.current_stream())
+    _lib.check(rc, "b200_w4a16_gemv_v2")
+    return out
+
+
+def w4a16_gemv_v2_config(splits: int = 0) -> None:
+    _lib.check(_lib.load().b200_w4a16_gemv_v2_config(int(splits)), "b200_w4a16_gemv_v2_config")
+
+
+GEMV_V2_MAX_M = 16
+
+
+def stream_copy_enabled() -> bool:
+    return os.environ.get("B200_W4A16_STREAM_COPY", "1") != "0"
+
+
+def w4a16_linear(x2: torch.Tensor, layer, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """Dispatch of AWQ/GPTQ apply(): decode batches (M <= 16) stream the repacked weight through
+    the GEMV, everything else runs the fused dequant + tcgen05 GEMM on the [K, N/8] layout."""
+    stream = getattr(layer, "b200_qweight_stream", None)
+    m = x2.shape[0]
+    if stream is not None and 1 <= m <= GEMV_V2_MAX_M and gemv_v2_supported(
+            m, layer.scales.shape[1], x2.shape[1], layer.w4a16_group_size):
+        return w4a16_gemv_v2(x2, stream, layer.b200_zeros, layer.scales, layer.w4a16_group_size, bias)
+    packed = layer.b200_qweight if hasattr(layer, "b200_qweight") else layer.qweight  # GPTQ / AWQ
+    return w4a16_gemm(x2, packed, layer.b200_zeros, layer.scales, layer.w4a16_group_size, bias)
 
 
 def w4a16_gemv_config(max_m: int = -1, splits: int = -1) -> None:

@@ -65,3 +65,33 @@ def test_fp8_block_mm_oracle_equals_reference_function():
                                         c["out"].dtype)
         # same tile order and fp32 accumulation as native_w8a8_block_fp8_matmul
         assert torch.equal(out, c["out"])
+
+
+def test_gemv_stream_layout_oracle_against_scalar_loops():
+    """The vectorised restatement of the decode GEMV's stream layout (our own format) against plain
+    loops written from the format description in csrc/w4a16_gemv2.cu."""
+    import numpy as np
+    import torch
+
+    from oracle import int4 as O
+
+    k, n = 128, 32
+    rs = np.random.RandomState(5)
+    qweight = torch.from_numpy(rs.randint(-2**31, 2**31, size=(k, n // 8), dtype=np.int64).astype(np.int32))
+    ints = O.unpack_awq_int4(qweight).numpy()
+    got = O.gemv_stream_layout_oracle(qweight).numpy().astype(np.int64) & 0xFFFFFFFF
+    order = [0, 2, 4, 6, 1, 3, 5, 7]
+    idx = 0
+    for nt in range(n // 16):
+        for kb in range(k // 64):
+            for lane in range(32):
+                g, t = lane >> 2, lane & 3
+                for j in range(4):
+                    col = nt * 16 + g + 8 * (j & 1)
+                    k0 = kb * 64 + (j >> 1) * 32 + 8 * t
+                    w = 0
+                    for i in range(8):
+                        w |= int(ints[k0 + order[i], col]) << (4 * i)
+                    assert got[idx] == w, (nt, kb, lane, j)
+                    idx += 1
+    assert idx == got.size

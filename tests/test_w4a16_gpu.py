@@ -219,3 +219,119 @@ def test_w4a16_gemv_integer_exact(dtype, gemv_cfg):
     gemv_cfg(16, 2)
     out = w4a16_gemm(x.cuda(), qw, zb, sc, group)
     assert torch.equal(out.cpu(), exact.to(dtype))
+
+
+# ---- decode GEMV, second generation (csrc/w4a16_gemv2.cu): stream layout + mma.sync ---------------
+@pytest.mark.parametrize("k,n", [(64, 16), (256, 272), (1024, 512), (5120, 3584)])
+def test_gemv_stream_repack_bit_exact(k, n):
+    from sglang_security_b200.layers.quantization.w4a16_kernel import gemv_stream_repack
+
+    qweight = _rand_i32((k, n // 8), k + n)
+    got = gemv_stream_repack(qweight.cuda()).cpu()
+    assert torch.equal(got, O.gemv_stream_layout_oracle(qweight))
+
+
+def test_gemv_stream_repack_unsupported_shapes():
+    from sglang_security_b200.layers.quantization.w4a16_kernel import gemv_stream_repack, gemv_v2_supported
+
+    assert gemv_stream_repack(_rand_i32((96, 4), 1).cuda()) is None      # K % 64
+    assert gemv_stream_repack(_rand_i32((64, 3), 1).cuda()) is None      # N % 16
+    assert not gemv_v2_supported(17, 256, 512, 128)
+    assert not gemv_v2_supported(4, 256, 512, 96)
+    assert gemv_v2_supported(16, 27648, 5120, 128) and gemv_v2_supported(1, 5120, 13824, 128)
+
+
+@pytest.fixture
+def gemv2_cfg():
+    from sglang_security_b200.layers.quantization.w4a16_kernel import w4a16_gemv_v2_config
+
+    yield w4a16_gemv_v2_config
+    w4a16_gemv_v2_config(0)
+
+
+@pytest.mark.parametrize("m", [1, 2, 7, 8, 9, 16])
+@pytest.mark.parametrize("k,n,group,splits", [(512, 256, 128, 0), (5120, 3584, 128, 0),
+                                              (2560, 5120, 128, 0), (1024, 288, 64, 8),
+                                              (256, 32, 32, 2), (13824, 5120, 128, 0),
+                                              (640, 2048, 128, 4), (5120, 27648, 128, 0),
+                                              (1024, 272, 1024, 1)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_w4a16_gemv_v2_matches_oracle(m, k, n, group, splits, dtype, gemv2_cfg):
+    """Stream-layout GEMV against x @ dequant (oracle) at the reference tolerance, at least as
+    close to the exact fp64 result as the dequant-GEMM, and run-to-run bit-identical (fixed
+    reduction order); covers empty cluster ranks, partial 128-column groups, groups of 32 / 64 /
+    128 / K, both token-tile counts and the cfg-4 TP = 2 shapes."""
+    from sglang_security_b200._lib import load
+    from sglang_security_b200.layers.quantization.w4a16_kernel import (gemv_stream_repack, w4a16_gemm,
+                                                                        w4a16_gemv_v2)
+
+    qweight, scales, qzeros = _awq_layer(k, n, group, dtype, seed=m * 3 + k + n, realistic=(n % 128 == 0))
+    g = torch.Generator().manual_seed(m + n)
+    x = torch.randn((m, k), generator=g).to(dtype)
+    bias = torch.randn((n,), generator=g).to(dtype)
+    big = m * k * n > 2 ** 30
+    dev = "cuda" if big else "cpu"
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = O.w4a16_linear_oracle(x.to(dev), O.awq_dequantize_oracle(
+        qweight.to(dev), scales.to(dev), qzeros.to(dev), group), bias.to(dev)).cpu()
+    qw, zb, sc = _prep(qweight, scales, qzeros, dtype)
+    stream = gemv_stream_repack(qw)
+    gemv2_cfg(splits)
+    out = w4a16_gemv_v2(x.cuda(), stream, zb, sc, group, bias.cuda())
+    assert b"w4a16_gemv2" in load().b200_last_variant()
+    assert torch.equal(out, w4a16_gemv_v2(x.cuda(), stream, zb, sc, group, bias.cuda()))
+    err = (out.cpu().float() - ref.float()).abs()
+    tol = 1e-2 * ref.float().abs() + 1e-2 * ref.float().abs().max()
+    assert (err <= tol).all(), (err.max().item(), ref.float().abs().max().item())
+    if not big:
+        out_big = w4a16_gemm(x.cuda(), qw, zb, sc, group, bias.cuda())
+        w_exact = (O.unpack_awq_int4(qweight).double() -
+                   O.unpack_awq_int4(qzeros).double().repeat_interleave(group, 0)) * \
+            scales.double().repeat_interleave(group, 0)
+        exact = x.double() @ w_exact + bias.double()
+        e_gemv = (out.cpu().double() - exact).abs().mean().item()
+        e_big = (out_big.cpu().double() - exact).abs().mean().item()
+        assert e_gemv <= 1.05 * e_big + 1e-6, (e_gemv, e_big)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m", [5, 13])
+def test_w4a16_gemv_v2_integer_exact(dtype, m, gemv2_cfg):
+    """INT4 unpacking through the stream layout is exact: unit scales and activations in
+    {-1, 0, 1} make every partial sum an integer below 2^24 and the result fit the 16-bit output
+    (f16: this also proves the 1/16 pre-scaling of the shift-free nibble pairs is exact)."""
+    from sglang_security_b200.layers.quantization.w4a16_kernel import gemv_stream_repack, w4a16_gemv_v2
+
+    k, n, group = 256, 512, 64
+    qweight = _rand_i32((k, n // 8), 31)
+    qzeros = _rand_i32((k // group, n // 8), 32)
+    scales = torch.ones((k // group, n), dtype=dtype)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(-1, 2, (m, k), generator=g).to(dtype)
+    w = O.unpack_awq_int4(qweight).long() - O.unpack_awq_int4(qzeros).long().repeat_interleave(group, 0)
+    exact = x.long() @ w
+    qw, zb, sc = _prep(qweight, scales, qzeros, dtype)
+    gemv2_cfg(2)
+    out = w4a16_gemv_v2(x.cuda(), gemv_stream_repack(qw), zb, sc, group)
+    assert torch.equal(out.cpu(), exact.to(dtype))
+
+
+def test_awq_method_decode_batches_take_the_stream_gemv():
+    from sglang_security_b200._lib import load
+    from sglang_security_b200.layers.linear import ColumnParallelLinear
+    from sglang_security_b200.layers.quantization.awq import AWQConfig
+
+    k, n, group, dtype = 512, 256, 128, torch.float16
+    qweight, scales, qzeros = _awq_layer(k, n, group, dtype, seed=3, realistic=True)
+    layer = ColumnParallelLinear(k, n, bias=False, params_dtype=dtype,
+                                 quant_config=AWQConfig(4, group, True), tp_rank=0, tp_size=1).cuda()
+    layer.qweight.data.copy_(qweight)
+    layer.qzeros.data.copy_(qzeros)
+    layer.scales.data.copy_(scales)
+    layer.quant_method.process_weights_after_loading(layer)
+    assert layer.b200_qweight_stream is not None
+    x = torch.randn((4, k), dtype=dtype, device="cuda")
+    layer(x)
+    assert b"w4a16_gemv2" in load().b200_last_variant()
+    layer(torch.randn((40, k), dtype=dtype, device="cuda"))
+    assert b"w4a16_gemv2" not in load().b200_last_variant()
