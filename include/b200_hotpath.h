@@ -127,6 +127,34 @@ int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
                            float k_scale, float v_scale, int dtype, void* workspace,
                            size_t workspace_bytes, int num_splits, void* stream);
 
+/* Fused decode tail: same operands and math as b200_attn_decode / b200_attn_decode_fp8kv, but the
+ * LAST CTA of every request to finish (ticket counter in `tickets`: uint32 [bs], zero before the
+ * first call, self-resetting, so CUDA-graph replays need no memset) merges the split partials of
+ * all heads itself — no b200_attn_merge launch — and, when q_out != NULL, also quantises the output
+ * row per token to e4m3 exactly as b200_fp8_quant_per_token would from the rounded 16-bit row
+ * (q_out [bs, q_out_stride] bytes, q_scales [bs] fp32): the o_proj input quantiser of
+ * Fp8LinearMethod.apply (fp8_utils.py:454-648) disappears from the decode step.  write_o = 0 skips
+ * the 16-bit output row when only q_out is consumed (ignored when num_splits == 1).
+ * b200_attn_decode_fused_supported: 1 when Hq x num_splits fits the tail's shared memory.        */
+int b200_attn_decode_fused(const void* q, int64_t q_stride, const void* k_cache,
+                           const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
+                           int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                           void* workspace, size_t workspace_bytes, int num_splits, void* tickets,
+                           void* q_out, int64_t q_out_stride, float* q_scales, int write_o,
+                           void* stream);
+int b200_attn_decode_fp8kv_fused(const void* q, int64_t q_stride, const void* k_cache,
+                                 const void* v_cache, int64_t kv_row_stride, void* o,
+                                 int64_t o_stride, const int32_t* req_to_token,
+                                 int64_t req_to_token_stride, const int64_t* req_pool_indices,
+                                 const int64_t* seq_lens, int bs, int Hq, int Hkv, int D, int Dv,
+                                 float scale, float logit_cap, float k_scale, float v_scale,
+                                 int dtype, void* workspace, size_t workspace_bytes, int num_splits,
+                                 void* tickets, void* q_out, int64_t q_out_stride, float* q_scales,
+                                 int write_o, void* stream);
+int b200_attn_decode_fused_supported(int Hq, int D, int num_splits, int fp8kv);
+
 /* Merge of split-KV partial states (replaces _fwd_kernel_stage2, decode_attention.py:497-557,
  * and merge_state_v2, sgl-kernel/csrc/attention/merge_attn_states.cu): exposed for tests.
  *   part_o   fp32 [bs, Hq, num_splits, Dv] ; part_lse fp32 [bs, Hq, num_splits] (log2 domain)  */

@@ -57,6 +57,17 @@ _SIGNATURES = {
                                  c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_int, c_int, c_float, c_float, c_int, c_void_p, c_size_t,
                                  c_int, c_void_p]),
+    "b200_attn_decode_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                       c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
+                                       c_int, c_int, c_int, c_float, c_float, c_int, c_void_p,
+                                       c_size_t, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_int,
+                                       c_void_p]),
+    "b200_attn_decode_fp8kv_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                             c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int,
+                                             c_int, c_int, c_int, c_int, c_float, c_float, c_float,
+                                             c_float, c_int, c_void_p, c_size_t, c_int, c_void_p,
+                                             c_void_p, c_int64, c_void_p, c_int, c_void_p]),
+    "b200_attn_decode_fused_supported": (c_int, [c_int, c_int, c_int, c_int]),
     "b200_attn_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int,
                                 c_int, c_int, c_int, c_int, c_void_p]),
     "b200_attn_extend": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64,

@@ -46,6 +46,14 @@ struct DecodeParams {
   float logit_cap;  // <= 0: disabled
   float v_scale;    // FP8 KV pool only: output multiplier (k_scale is folded into qk_scale)
   int pdl_late;
+  // Fused tail (b200_attn_decode*_fused): the LAST CTA of a request to finish (ticket counter)
+  // merges the split partials of all its heads and, optionally, quantises the output row to e4m3
+  // per token — the merge kernel and the o_proj input quantiser disappear from the step.
+  unsigned* tickets;     // [bs], zero before the first launch, self-resetting; null = no tail
+  uint8_t* q_out;        // [bs, q_out_stride] e4m3 or null
+  int64_t q_out_stride;
+  float* q_scales;       // [bs]
+  int write_o;           // 0: the 16-bit output row is not needed (only q_out is consumed)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -135,13 +143,162 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
   return r;
 }
 
+
+// ---- fused tail: merge of the split partials (+ per-token FP8 quantisation) by the last CTA --------
+// Every CTA of request b that has work publishes its partials, fences and takes a ticket; the one
+// that draws the last ticket (nvalid splits x gridDim.y CTAs) sees all partials of the request
+// (threadFenceReduction pattern) and finishes the row: same arithmetic as attn_merge_kernel
+// (num * 1/den, one rounding to T) followed by fp8_quant_per_token_kernel's (scale = amax / 448,
+// q = sat(x * (1/scale)) on the ROUNDED 16-bit values), so the bytes equal merge + quantiser.
+// Shared memory (the idle pipeline ring): weights [Hq][num_splits] + 1/den [Hq] fp32, then the row as T.
+__host__ __device__ inline size_t decode_tail_wgt_bytes(int Hq, int num_splits) {
+  return (static_cast<size_t>(Hq) * (num_splits + 1) * 4 + 15) & ~static_cast<size_t>(15);
+}
+__host__ __device__ inline size_t decode_tail_smem_bytes(int Hq, int D, int num_splits) {
+  return decode_tail_wgt_bytes(Hq, num_splits) + static_cast<size_t>(Hq) * D * 2;
+}
+
+struct TailDev {
+  unsigned* tickets;
+  uint8_t* q_out;
+  int64_t q_out_stride;
+  float* q_scales;
+  void* o;
+  int64_t o_stride;
+  const float* part_o;
+  const float* part_lse;
+  int Hq, num_splits, write_o;
+};
+__device__ __forceinline__ TailDev tail_of(const DecodeParams& p) {
+  TailDev t;
+  t.tickets = p.tickets;
+  t.q_out = p.q_out;
+  t.q_out_stride = p.q_out_stride;
+  t.q_scales = p.q_scales;
+  t.o = p.o;
+  t.o_stride = p.o_stride;
+  t.part_o = p.part_o;
+  t.part_lse = p.part_lse;
+  t.Hq = p.Hq;
+  t.num_splits = p.num_splits;
+  t.write_o = p.write_o;
+  return t;
+}
+
+template <typename T, int THREADS>
+__device__ __noinline__ void decode_fused_tail(const TailDev p, int b, int nvalid, int D,
+                                               uint8_t* smem) {
+  __shared__ unsigned s_last;
+  __shared__ float s_red[THREADS / 32];
+  // bar.sync orders every thread's partial / output stores before thread 0's gpu-scope acq_rel
+  // ticket draw (release is cumulative over what the barrier made visible to thread 0); on the
+  // last CTA the same draw is the acquire, and the second barrier hands it to the other threads.
+  __syncthreads();   // also: the pipeline ring is idle from here on
+  if (threadIdx.x == 0) {
+    const unsigned total = static_cast<unsigned>(nvalid) * gridDim.y;
+    unsigned prev;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;\n"
+                 : "=r"(prev) : "l"(p.tickets + b) : "memory");
+    const bool last = prev + 1 == total;
+    if (last) p.tickets[b] = 0u;  // every other CTA of this request has drawn: safe to re-arm
+    s_last = last ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  const int Hq = p.Hq, NS = p.num_splits;
+  const int n4 = Hq * D / 4;
+  float* wgt = reinterpret_cast<float*>(smem);             // [Hq][NS] unnormalised weights
+  float* inv_den = wgt + Hq * NS;                           // [Hq]
+  T* row = reinterpret_cast<T*>(smem + decode_tail_wgt_bytes(Hq, NS));
+  if (NS > 1) {
+    for (int h = threadIdx.x; h < Hq; h += THREADS) {
+      const float* lse = p.part_lse + (static_cast<int64_t>(b) * Hq + h) * NS;
+      float M = -INFINITY;
+      for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldcg(lse + s));
+      float den = 0.f;
+      for (int s = 0; s < nvalid; ++s) {
+        const float f = fast_exp2(__ldcg(lse + s) - M);
+        wgt[h * NS + s] = f;
+        den += f;
+      }
+      inv_den[h] = 1.f / den;
+    }
+    __syncthreads();
+  }
+  T* orow = static_cast<T*>(p.o) + static_cast<int64_t>(b) * p.o_stride;
+  float amax = 0.f;
+  for (int it = threadIdx.x; it < n4; it += THREADS) {
+    const int e0 = it * 4, h = e0 / D, d = e0 - h * D;
+    float v[4];
+    if (NS > 1) {
+      const float* po = p.part_o + (static_cast<int64_t>(b) * Hq + h) * NS * D + d;
+      float num[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int s = 0; s < nvalid; ++s) {
+        const float w = wgt[h * NS + s];
+        const float4 x = __ldcg(reinterpret_cast<const float4*>(po + s * D));
+        num[0] += w * x.x;
+        num[1] += w * x.y;
+        num[2] += w * x.z;
+        num[3] += w * x.w;
+      }
+      const float inv = inv_den[h];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) v[e] = to_float<T>(from_float<T>(num[e] * inv));
+      if (p.write_o) {
+        uint2 pk;
+        pk.x = pack2<T>(v[0], v[1]);
+        pk.y = pack2<T>(v[2], v[3]);
+        *reinterpret_cast<uint2*>(orow + e0) = pk;
+      }
+    } else {
+      const uint2 pk = __ldcg(reinterpret_cast<const uint2*>(orow + e0));
+      const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
+      v[0] = a.x; v[1] = a.y; v[2] = c.x; v[3] = c.y;
+    }
+    if (p.q_out) {
+      uint2 pk;
+      pk.x = pack2<T>(v[0], v[1]);
+      pk.y = pack2<T>(v[2], v[3]);
+      *reinterpret_cast<uint2*>(row + e0) = pk;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) amax = fmaxf(amax, fabsf(v[e]));
+    }
+  }
+  if (!p.q_out) return;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = amax;
+  __syncthreads();
+  amax = s_red[0];
+#pragma unroll
+  for (int w = 1; w < THREADS / 32; ++w) amax = fmaxf(amax, s_red[w]);
+  const float scale = amax / 448.0f;
+  if (threadIdx.x == 0) p.q_scales[b] = scale;
+  const float inv = scale > 0.f ? 1.0f / scale : 0.f;
+  uint8_t* qrow = p.q_out + static_cast<int64_t>(b) * p.q_out_stride;
+  for (int it = threadIdx.x; it < n4; it += THREADS) {
+    const uint2 pk = *reinterpret_cast<const uint2*>(row + it * 4);
+    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
+    const float v[4] = {a.x, a.y, c.x, c.y};
+    uint32_t q = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float x = fmaxf(fminf(v[e] * inv, 448.0f), -448.0f);
+      uint16_t r;
+      asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(x));
+      q |= static_cast<uint32_t>(r & 0xffu) << (8 * e);
+    }
+    *reinterpret_cast<uint32_t*>(qrow + it * 4) = q;
+  }
+}
+
 }  // namespace b200
 #include "attn_decode_fp8.cuh"
 namespace b200 {
 
 // HI: the tile holds more than 8 heads (rows 8..15 of the MMA are live).
-template <typename T, int D, int NT, int STAGES, int NW, bool HI>
-__global__ void __launch_bounds__(NW * 32)
+template <typename T, int D, int NT, int STAGES, int NW, bool HI, bool TAIL>
+__global__ void __launch_bounds__(NW * 32, TAIL ? 4 : 0)
 attn_decode_mma_kernel(const DecodeParams p) {
   using C = MmaCfg<D, NT, STAGES, NW>;
   constexpr int CPR = C::CPR, RPG = C::RPG, ROW_BYTES = C::ROW_BYTES;
@@ -413,6 +570,7 @@ attn_decode_mma_kernel(const DecodeParams p) {
       if (d == 0) p.part_lse[pidx] = M + log2f(den);
     }
   }
+  if constexpr (TAIL) decode_fused_tail<T, NW * 32>(tail_of(p), b, ceil_div(len, chunk), D, smem);
 }
 
 // Merge of split partials: one CTA per (query head, request).
@@ -458,10 +616,41 @@ static int decode_ctas_per_sm(int D) {
   return n < 1 ? 1 : n;
 }
 
+// launcher of the fused-tail instantiations (own attribute flag per kernel through the template)
+template <typename C>
+static int launch_decode_any(void (*kern)(const DecodeParams), const DecodeParams& p, cudaStream_t st,
+                             const char* timer_name, const char* kernel_name) {
+  static void (*configured[64])(const DecodeParams) = {};
+  static int n_configured = 0;
+  bool done = false;
+  for (int i = 0; i < n_configured; ++i) done |= configured[i] == kern;
+  if (!done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+    if (n_configured < 64) configured[n_configured++] = kern;
+  }
+  dim3 grid(p.num_splits, p.Hkv * p.head_tiles, p.bs);
+  {
+    ScopedKernelTimer timer(timer_name, st);
+    B200_CUDA_OK(launch_kernel(kern, grid, dim3(C::THREADS), C::SMEM_BYTES, st, 1,
+                               pdl_family(p.bs, kPdlAttn), p));
+  }
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: launch failed: %s", kernel_name, cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return 2;
+  }
+  return 0;
+}
+
 template <typename T, int D, bool HI>
 static int launch_decode(const DecodeParams& p, cudaStream_t st) {
   using C = MmaCfg<D, kNT, kStages, kNW>;
-  auto kern = attn_decode_mma_kernel<T, D, kNT, kStages, kNW, HI>;
+  if (p.tickets) return launch_decode_any<C>(attn_decode_mma_kernel<T, D, kNT, kStages, kNW, HI, true>, p, st,
+                                             "attn_decode_split", "attn_decode_mma_kernel");
+  auto kern = attn_decode_mma_kernel<T, D, kNT, kStages, kNW, HI, false>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -501,7 +690,9 @@ static int fp8kv_stages() {
 template <typename T, int D, bool HI, int ST>
 static int launch_decode_fp8kv_st(const DecodeParams& p, cudaStream_t st) {
   using C = Fp8KvCfg<D, kNT8, ST, kNW>;
-  auto kern = attn_decode_fp8kv_kernel<T, D, kNT8, ST, kNW, HI>;
+  if (p.tickets) return launch_decode_any<C>(attn_decode_fp8kv_kernel<T, D, kNT8, ST, kNW, HI, true>, p, st,
+                                             "attn_decode_fp8kv", "attn_decode_fp8kv_kernel");
+  auto kern = attn_decode_fp8kv_kernel<T, D, kNT8, ST, kNW, HI, false>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -532,6 +723,44 @@ static int dispatch_decode_fp8kv(const DecodeParams& p, int D, int G, cudaStream
     return G > 8 ? launch_decode_fp8kv<T, 64, true>(p, st) : launch_decode_fp8kv<T, 64, false>(p, st);
   set_error("b200_attn_decode_fp8kv: unsupported head_dim %d (supported: 64, 128)", D);
   return 1;
+}
+
+// Host side of the fused tail (see decode_fused_tail).
+struct DecodeTail {
+  void* tickets;
+  void* q_out;
+  int64_t q_out_stride;
+  float* q_scales;
+  int write_o;
+};
+
+static int apply_tail(DecodeParams& p, const DecodeTail* tail, int D, size_t ring_bytes,
+                      const char* who) {
+  p.tickets = nullptr;
+  p.q_out = nullptr;
+  p.q_out_stride = 0;
+  p.q_scales = nullptr;
+  p.write_o = 1;
+  if (!tail) return 0;
+  B200_REQUIRE(tail->tickets, "%s: null ticket buffer", who);
+  B200_REQUIRE((tail->q_out == nullptr) == (tail->q_scales == nullptr),
+               "%s: q_out and q_scales go together", who);
+  B200_REQUIRE(tail->q_out || tail->write_o, "%s: nothing to produce (no q_out, write_o = 0)", who);
+  B200_REQUIRE(!tail->q_out || (tail->q_out_stride % 4 == 0 &&
+                                (reinterpret_cast<uintptr_t>(tail->q_out) & 3u) == 0),
+               "%s: q_out must be 4-byte aligned with q_out_stride %% 4 == 0", who);
+  B200_REQUIRE(p.o_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(p.o) & 7u) == 0,
+               "%s: o must be 8-byte aligned with o_stride %% 4 == 0", who);
+  B200_REQUIRE(decode_tail_smem_bytes(p.Hq, D, p.num_splits) <= ring_bytes,
+               "%s: Hq=%d x num_splits=%d does not fit the tail's shared memory "
+               "(use b200_attn_decode_fused_supported)", who, p.Hq, p.num_splits);
+  p.tickets = static_cast<unsigned*>(tail->tickets);
+  p.q_out = static_cast<uint8_t*>(tail->q_out);
+  p.q_out_stride = tail->q_out_stride;
+  p.q_scales = tail->q_scales;
+  // with one split the CTAs write the 16-bit row themselves and the tail reads it back
+  p.write_o = (tail->write_o || p.num_splits == 1) ? 1 : 0;
+  return 0;
 }
 
 }  // namespace b200
@@ -573,12 +802,13 @@ int b200_attn_decode_num_splits(int bs, int Hkv, int group, int D, int64_t avg_l
   return best;
 }
 
-int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
-                     int64_t kv_row_stride, void* o, int64_t o_stride,
-                     const int32_t* req_to_token, int64_t req_to_token_stride,
-                     const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
-                     int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
-                     void* workspace, size_t workspace_bytes, int num_splits, void* stream) {
+static int attn_decode_impl(const void* q, int64_t q_stride, const void* k_cache,
+                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                            const int32_t* req_to_token, int64_t req_to_token_stride,
+                            const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
+                            int Hq, int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                            void* workspace, size_t workspace_bytes, int num_splits, void* stream,
+                            const b200::DecodeTail* tail) {
   using namespace b200;
   if (bs == 0) return 0;
   B200_REQUIRE(q && k_cache && v_cache && o && req_to_token && req_pool_indices && seq_lens,
@@ -625,25 +855,62 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
   p.part_o = static_cast<float*>(workspace);
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
 
+  if (int rc = apply_tail(p, tail, D, /*ring_bytes=*/MmaCfg<128, kNT, kStages, kNW>::SMEM_BYTES * D / 128,
+                          "b200_attn_decode_fused"))
+    return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = dtype == B200_BF16 ? dispatch_decode<__nv_bfloat16>(p, D, G, st)
                               : dispatch_decode<__half>(p, D, G, st);
   if (rc) return rc;
-  if (num_splits > 1)
+  if (num_splits > 1 && !tail)
     return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
                            decode_align(), dtype, stream);
   return 0;
 }
 
-int b200_attn_decode_fp8kv_split_align(void) { return b200::decode_align_fp8kv(); }
+int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                     int64_t kv_row_stride, void* o, int64_t o_stride,
+                     const int32_t* req_to_token, int64_t req_to_token_stride,
+                     const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
+                     int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                     void* workspace, size_t workspace_bytes, int num_splits, void* stream) {
+  return attn_decode_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride, req_to_token,
+                          req_to_token_stride, req_pool_indices, seq_lens, bs, Hq, Hkv, D, Dv, scale,
+                          logit_cap, dtype, workspace, workspace_bytes, num_splits, stream, nullptr);
+}
 
-int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+int b200_attn_decode_fused(const void* q, int64_t q_stride, const void* k_cache,
                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
                            const int32_t* req_to_token, int64_t req_to_token_stride,
-                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
-                           int Hq, int Hkv, int D, int Dv, float scale, float logit_cap,
-                           float k_scale, float v_scale, int dtype, void* workspace,
-                           size_t workspace_bytes, int num_splits, void* stream) {
+                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
+                           int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                           void* workspace, size_t workspace_bytes, int num_splits, void* tickets,
+                           void* q_out, int64_t q_out_stride, float* q_scales, int write_o,
+                           void* stream) {
+  b200::DecodeTail tail = {tickets, q_out, q_out_stride, q_scales, write_o};
+  return attn_decode_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride, req_to_token,
+                          req_to_token_stride, req_pool_indices, seq_lens, bs, Hq, Hkv, D, Dv, scale,
+                          logit_cap, dtype, workspace, workspace_bytes, num_splits, stream, &tail);
+}
+
+int b200_attn_decode_fused_supported(int Hq, int D, int num_splits, int fp8kv) {
+  using namespace b200;
+  if (D != 64 && D != 128) return 0;
+  const size_t ring = fp8kv ? Fp8KvCfg<128, kNT8, 2, kNW>::SMEM_BYTES * static_cast<size_t>(D) / 128
+                            : MmaCfg<128, kNT, kStages, kNW>::SMEM_BYTES * static_cast<size_t>(D) / 128;
+  return decode_tail_smem_bytes(Hq, D, num_splits) <= ring ? 1 : 0;
+}
+
+int b200_attn_decode_fp8kv_split_align(void) { return b200::decode_align_fp8kv(); }
+
+static int attn_decode_fp8kv_impl(const void* q, int64_t q_stride, const void* k_cache,
+                                  const void* v_cache, int64_t kv_row_stride, void* o,
+                                  int64_t o_stride, const int32_t* req_to_token,
+                                  int64_t req_to_token_stride, const int64_t* req_pool_indices,
+                                  const int64_t* seq_lens, int bs, int Hq, int Hkv, int D, int Dv,
+                                  float scale, float logit_cap, float k_scale, float v_scale,
+                                  int dtype, void* workspace, size_t workspace_bytes, int num_splits,
+                                  void* stream, const b200::DecodeTail* tail) {
   using namespace b200;
   if (bs == 0) return 0;
   B200_REQUIRE(q && k_cache && v_cache && o && req_to_token && req_pool_indices && seq_lens,
@@ -689,14 +956,46 @@ int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
   { static const char* e = std::getenv("B200_PDL_LATE"); p.pdl_late = e ? std::atoi(e) : 1; }
   p.part_o = static_cast<float*>(workspace);
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
+  if (int rc = apply_tail(p, tail, D, /*ring_bytes=*/Fp8KvCfg<128, kNT8, 2, kNW>::SMEM_BYTES * D / 128,
+                          "b200_attn_decode_fp8kv_fused"))
+    return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, st)
                                     : dispatch_decode_fp8kv<__half>(p, D, G, st);
   if (rc) return rc;
-  if (num_splits > 1)
+  if (num_splits > 1 && !tail)
     return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
                            decode_align_fp8kv(), dtype, stream);
   return 0;
+}
+
+int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                           const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                           const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
+                           int Hq, int Hkv, int D, int Dv, float scale, float logit_cap,
+                           float k_scale, float v_scale, int dtype, void* workspace,
+                           size_t workspace_bytes, int num_splits, void* stream) {
+  return attn_decode_fp8kv_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride,
+                                req_to_token, req_to_token_stride, req_pool_indices, seq_lens, bs, Hq,
+                                Hkv, D, Dv, scale, logit_cap, k_scale, v_scale, dtype, workspace,
+                                workspace_bytes, num_splits, stream, nullptr);
+}
+
+int b200_attn_decode_fp8kv_fused(const void* q, int64_t q_stride, const void* k_cache,
+                                 const void* v_cache, int64_t kv_row_stride, void* o,
+                                 int64_t o_stride, const int32_t* req_to_token,
+                                 int64_t req_to_token_stride, const int64_t* req_pool_indices,
+                                 const int64_t* seq_lens, int bs, int Hq, int Hkv, int D, int Dv,
+                                 float scale, float logit_cap, float k_scale, float v_scale,
+                                 int dtype, void* workspace, size_t workspace_bytes, int num_splits,
+                                 void* tickets, void* q_out, int64_t q_out_stride, float* q_scales,
+                                 int write_o, void* stream) {
+  b200::DecodeTail tail = {tickets, q_out, q_out_stride, q_scales, write_o};
+  return attn_decode_fp8kv_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride,
+                                req_to_token, req_to_token_stride, req_pool_indices, seq_lens, bs, Hq,
+                                Hkv, D, Dv, scale, logit_cap, k_scale, v_scale, dtype, workspace,
+                                workspace_bytes, num_splits, stream, &tail);
 }
 
 int b200_attn_decode_split_align(int D, int group) {

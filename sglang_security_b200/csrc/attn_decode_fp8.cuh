@@ -78,8 +78,8 @@ __device__ __forceinline__ void q4_to_f16<__nv_bfloat16>(const __nv_bfloat16* q,
   hi = *reinterpret_cast<const uint32_t*>(&hb);
 }
 
-template <typename T, int D, int NT, int STAGES, int NW, bool HI>
-__global__ void __launch_bounds__(NW * 32)
+template <typename T, int D, int NT, int STAGES, int NW, bool HI, bool TAIL>
+__global__ void __launch_bounds__(NW * 32, TAIL ? 4 : 0)
 attn_decode_fp8kv_kernel(const DecodeParams p) {
   using C = Fp8KvCfg<D, NT, STAGES, NW>;
   constexpr int CPR = C::CPR, RPG = C::RPG, RB = C::RB;
@@ -366,6 +366,7 @@ attn_decode_fp8kv_kernel(const DecodeParams p) {
       if (d == 0) p.part_lse[pidx] = M + log2f(den);
     }
   }
+  if constexpr (TAIL) decode_fused_tail<T, NW * 32>(tail_of(p), b, ceil_div(len, chunk), D, smem);
 }
 
 }  // namespace b200

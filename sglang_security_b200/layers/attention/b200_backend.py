@@ -6,7 +6,9 @@ implementation of the same interface, triton_backend.py:151-835).  It indexes
 `req_to_token_pool.req_to_token` and the `MHATokenToKVPool` buffers in place (layouts unchanged)
 and calls the sm_100a kernels through the C-ABI (include/b200_hotpath.h):
 
-  forward_decode : b200_kv_write -> b200_attn_decode (split-KV gather kernel + merge kernel)
+  forward_decode : b200_kv_write -> b200_attn_decode_fused (split-KV gather kernel whose last CTA per
+                   request merges the splits and, on request, quantises the row for o_proj);
+                   B200_ATTN_FUSED_TAIL=0 restores split kernel + merge kernel
   forward_extend : b200_kv_write -> b200_attn_extend (tcgen05 prefix rectangle + causal triangle)
 
 All per-step metadata is computed without a device->host sync; buffers are persistent so the
@@ -16,6 +18,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass, field
 from typing import Dict, Optional
+
+import os
 
 import torch
 
@@ -70,6 +74,18 @@ class B200AttnBackend(AttentionBackend):
         self._workspace: Optional[torch.Tensor] = None
         self._graph_workspace: Optional[torch.Tensor] = None
         self._graph_max_bs = 0
+        # fused decode tail (merge + optional o_proj input quantisation by the last CTA of a request)
+        self.fused_tail = os.environ.get("B200_ATTN_FUSED_TAIL", "1") != "0"
+        self._tickets = torch.zeros(4096, dtype=torch.int32, device=self.device)
+
+    def _ticket_buffer(self, bs: int) -> torch.Tensor:
+        if self._tickets.numel() < bs:
+            if torch.cuda.is_current_stream_capturing():
+                raise _lib.B200Error("B200AttnBackend: ticket buffer too small during graph capture "
+                                     "(call init_cuda_graph_state with the largest batch first)")
+            self._tickets = torch.zeros(max(bs, 2 * self._tickets.numel()), dtype=torch.int32,
+                                        device=self.device)
+        return self._tickets
 
     # ------------------------------------------------------------------ metadata
     def _num_splits(self, bs: int, head_dim: int, avg_len: int) -> int:
@@ -123,6 +139,7 @@ class B200AttnBackend(AttentionBackend):
     # ------------------------------------------------------------------ CUDA graph hooks
     def init_cuda_graph_state(self, max_bs: int):
         self._graph_max_bs = max_bs
+        self._ticket_buffer(max_bs)
         max_splits = 64
         need = self.lib.b200_attn_decode_workspace_bytes(max_bs, self.num_head, self.v_head_dim,
                                                          max_splits)
@@ -205,7 +222,11 @@ class B200AttnBackend(AttentionBackend):
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("B200AttnBackend: cross-attention layers are not implemented")
 
-    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True,
+                       fp8_out: bool = False):
+        """fp8_out (B200 extension, default off = the reference contract): also quantise the output
+        row per token to e4m3 inside the attention kernel and return a QuantizedActivation for a
+        per-token FP8 o_proj, instead of the 16-bit tensor + a separate quantiser launch."""
         hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
         d, dv = layer.qk_head_dim, layer.v_head_dim
         q = q.reshape(-1, hq * d)
@@ -220,7 +241,7 @@ class B200AttnBackend(AttentionBackend):
             k_cache = pool.get_key_buffer(layer.layer_id)
             v_cache = pool.get_value_buffer(layer.layer_id)
         if bs == 0:
-            return o
+            return self._maybe_quant(o, fp8_out)
         self._check_layer(layer)
         md = self.forward_metadata
         req_to_token = forward_batch.req_to_token_pool.req_to_token
@@ -229,33 +250,54 @@ class B200AttnBackend(AttentionBackend):
         # kernels read int64, so convert once per forward and hold the copies in the metadata
         req_pool_indices = md.as_dtype(forward_batch.req_pool_indices, torch.int64)
         seq_lens = md.as_dtype(forward_batch.seq_lens, torch.int64)
-        if k_cache.dtype == torch.float8_e4m3fn:
-            ks, vs = self._kv_scales(layer)
-            rc = self.lib.b200_attn_decode_fp8kv(
-                q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
-                k_cache.stride(0), o.data_ptr(), o.stride(0), req_to_token.data_ptr(),
-                req_to_token.stride(0), req_pool_indices.data_ptr(),
-                seq_lens.data_ptr(), bs, hq, hkv, d, dv,
-                float(layer.scaling), float(layer.logit_cap or 0.0),
-                1.0 if ks is None else ks, 1.0 if vs is None else vs, _lib.dtype_code(q.dtype),
-                _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits,
-                _lib.current_stream())
-            _lib.check(rc, "b200_attn_decode_fp8kv")
-            return o
-        if k_cache.dtype != q.dtype:
+        fp8kv = k_cache.dtype == torch.float8_e4m3fn
+        if not fp8kv and k_cache.dtype != q.dtype:
             raise _lib.B200Error(
                 f"B200AttnBackend.forward_decode: KV cache dtype {k_cache.dtype} != q dtype "
                 f"{q.dtype} (supported pools: the activation dtype or float8_e4m3fn)")
-        rc = self.lib.b200_attn_decode(
-            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
-            o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
-            req_pool_indices.data_ptr(), seq_lens.data_ptr(), bs, hq, hkv, d, dv,
-            float(layer.scaling), float(layer.logit_cap or 0.0), _lib.dtype_code(q.dtype),
-            _lib.ptr(ws), 0 if ws is None else ws.numel(), md.num_splits, _lib.current_stream())
-        _lib.check(rc, "b200_attn_decode")
-        return o
+        common = (q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                  k_cache.stride(0), o.data_ptr(), o.stride(0), req_to_token.data_ptr(),
+                  req_to_token.stride(0), req_pool_indices.data_ptr(), seq_lens.data_ptr(), bs, hq,
+                  hkv, d, dv, float(layer.scaling), float(layer.logit_cap or 0.0))
+        if fp8kv:
+            ks, vs = self._kv_scales(layer)
+            common = common + (1.0 if ks is None else ks, 1.0 if vs is None else vs)
+        common = common + (_lib.dtype_code(q.dtype), _lib.ptr(ws), 0 if ws is None else ws.numel(),
+                           md.num_splits)
+        # the tail only pays when it replaces a launch: the merge (splits > 1) or the quantiser
+        fused = (self.fused_tail and (md.num_splits > 1 or fp8_out) and
+                 self.lib.b200_attn_decode_fused_supported(hq, dv, md.num_splits, 1 if fp8kv else 0))
+        if fused:
+            qa = sa = None
+            if fp8_out:
+                qa = torch.empty((bs, hq * dv), dtype=torch.float8_e4m3fn, device=q.device)
+                sa = torch.empty((bs, 1), dtype=torch.float32, device=q.device)
+            fn = self.lib.b200_attn_decode_fp8kv_fused if fp8kv else self.lib.b200_attn_decode_fused
+            rc = fn(*common, self._ticket_buffer(bs).data_ptr(), _lib.ptr(qa),
+                    0 if qa is None else qa.stride(0), _lib.ptr(sa), 0 if fp8_out else 1,
+                    _lib.current_stream())
+            _lib.check(rc, "b200_attn_decode_fused")
+            if fp8_out:
+                from ..quantization.fp8_utils import QuantizedActivation
 
-    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+                return QuantizedActivation(qa, sa, q.dtype)
+            return o
+        fn = self.lib.b200_attn_decode_fp8kv if fp8kv else self.lib.b200_attn_decode
+        rc = fn(*common, _lib.current_stream())
+        _lib.check(rc, "b200_attn_decode")
+        return self._maybe_quant(o, fp8_out)
+
+    @staticmethod
+    def _maybe_quant(o, fp8_out):
+        if not fp8_out:
+            return o
+        from ..quantization.fp8_kernel import sglang_per_token_quant_fp8 as per_token_quant_fp8
+        from ..quantization.fp8_utils import QuantizedActivation
+
+        qa, sa = per_token_quant_fp8(o)
+        return QuantizedActivation(qa, sa, o.dtype)
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **_):
         hq, hkv = layer.tp_q_head_num, layer.tp_k_head_num
         d, dv = layer.qk_head_dim, layer.v_head_dim
         q = q.reshape(-1, hq * d)

@@ -94,7 +94,13 @@ class B200DecoderLayer(nn.Module):
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
         if self.fuse:
             self.rotary_emb.forward_with_kv_write(positions, q, k, v, self.attn, forward_batch)
-            a = self.attn(q, k, v, forward_batch, save_kv_cache=False)
+            # decode with a per-token FP8 o_proj: the attention kernel's tail quantises its own
+            # output row (same bytes as the stand-alone quantiser), one launch less per layer
+            if (self.fp8_mode == "token" and forward_batch.forward_mode.is_decode() and
+                    getattr(forward_batch.attn_backend, "fused_tail", False)):
+                a = self.attn(q, k, v, forward_batch, save_kv_cache=False, fp8_out=True)
+            else:
+                a = self.attn(q, k, v, forward_batch, save_kv_cache=False)
         else:
             q, k = self.rotary_emb(positions, q, k)
             a = self.attn(q, k, v, forward_batch)

@@ -48,7 +48,8 @@ def make_model_runner(case, device="cuda", layer_num=1, num_kv_splits=0):
                            server_args=SimpleNamespace(b200_attention_num_kv_splits=num_kv_splits))
 
 
-def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype=None):
+def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype=None,
+             fused_tail=None, fp8_out=False, repeat=1):
     """CUDA path: B200AttnBackend through RadixAttention.forward, KV write included."""
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
     from sglang_security_b200.layers.radix_attention import RadixAttention
@@ -57,6 +58,8 @@ def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype
     dev = "cuda"
     mr = make_model_runner(case, dev, num_kv_splits=num_kv_splits)
     backend = B200AttnBackend(mr)
+    if fused_tail is not None:
+        backend.fused_tail = fused_tail
     layer = RadixAttention(case.hq, case.d, float(case.d) ** -0.5, case.hkv, 0, logit_cap=logit_cap)
     t = case.q.shape[0]
     if strided_qkv:
@@ -82,8 +85,13 @@ def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype
         extend_num_tokens=t, req_to_token_pool=mr.req_to_token_pool,
         token_to_kv_pool=mr.token_to_kv_pool, attn_backend=backend)
     backend.init_forward_metadata(fb)
-    o = layer(q, k, v, fb)
+    kw = {"fp8_out": True} if fp8_out else {}
+    for _ in range(repeat):  # repeats re-use the backend's ticket buffer (self-resetting counters)
+        o = layer(q, k, v, fb, **kw)
     torch.cuda.synchronize()
+    if fp8_out:
+        return (o.q.cpu(), o.scale.cpu()), mr.token_to_kv_pool.k_buffer[0].cpu(), \
+            mr.token_to_kv_pool.v_buffer[0].cpu()
     return o.cpu(), mr.token_to_kv_pool.k_buffer[0].cpu(), mr.token_to_kv_pool.v_buffer[0].cpu()
 
 

@@ -53,7 +53,7 @@ def test_kv_write_fp8_bit_exact(dtype, scales):
     assert torch.equal(qkv.cpu()[:, :hkv * d], k.reshape(t, -1))  # source left untouched
 
 
-def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0):
+def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0, fused_tail=None, fp8_out=False):
     """-> (o_gpu, o_oracle, k bytes gpu, k bytes oracle)"""
     import harness
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
@@ -85,6 +85,8 @@ def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0):
     pool.k_buffer[0].copy_(init_k)
     pool.v_buffer[0].copy_(init_v)
     backend = B200AttnBackend(mr)
+    if fused_tail is not None:
+        backend.fused_tail = fused_tail
     t = case.q.shape[0]
     qkv = torch.cat([case.q, case.k_new.reshape(t, -1), case.v_new.reshape(t, -1)], dim=1).cuda()
     q, k, v = qkv.split([case.hq * case.d, case.hkv * case.d, case.hkv * case.d], dim=-1)
@@ -94,6 +96,11 @@ def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0):
                       seq_lens_cpu=case.seq_lens, req_to_token_pool=mr.req_to_token_pool,
                       token_to_kv_pool=pool, attn_backend=backend)
     backend.init_forward_metadata(fb)
+    if fp8_out:
+        for _ in range(2):
+            o = layer(q, k, v, fb, save_kv_cache=False if _ else True, fp8_out=True)
+        torch.cuda.synchronize()
+        return (o.q.cpu(), o.scale.cpu()), o_ref.reshape(t, -1), pool.k_buffer[0].cpu(), ref.k_buffer[0]
     o = layer(q, k, v, fb)
     torch.cuda.synchronize()
     return o.cpu(), o_ref.reshape(t, -1), pool.k_buffer[0].cpu(), ref.k_buffer[0]
@@ -162,6 +169,8 @@ def test_extend_fp8kv_matches_oracle(hq, hkv, d, scales):
     pool.k_buffer[0].copy_(init_k)
     pool.v_buffer[0].copy_(init_v)
     backend = B200AttnBackend(mr)
+    if fused_tail is not None:
+        backend.fused_tail = fused_tail
     t = case.q.shape[0]
     qkv = torch.cat([case.q, case.k_new.reshape(t, -1), case.v_new.reshape(t, -1)], dim=1).cuda()
     q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
@@ -181,3 +190,19 @@ def test_extend_fp8kv_matches_oracle(hq, hkv, d, scales):
     assert torch.equal(pool.v_buffer[0].cpu(), ref.v_buffer[0])
     st = harness.error_stats(o.cpu(), o_ref.reshape(t, -1))
     assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, st
+
+
+@pytest.mark.parametrize("splits", [1, 3])
+def test_decode_fp8kv_fused_tail_equals_unfused(splits):
+    """FP8-KV decode: fused merge + per-token quantisation tail == split + merge (+ quantiser)."""
+    from sglang_security_b200.layers.quantization.fp8_kernel import sglang_per_token_quant_fp8
+
+    case = scenarios.make_attention_case(seed=41 + splits, hq=32, hkv=8, d=128,
+                                         seq_lens=[1, 95, 96, 97, 700, 1025], shared_prefix=20)
+    o_plain, _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=False)
+    o_fused, _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True)
+    assert torch.equal(o_plain.view(torch.int16), o_fused.view(torch.int16))
+    (qa, sa), _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True, fp8_out=True)
+    q_ref, s_ref = sglang_per_token_quant_fp8(o_plain.cuda())
+    assert torch.equal(sa, s_ref.cpu())
+    assert torch.equal(qa.view(torch.uint8), q_ref.cpu().view(torch.uint8))

@@ -148,13 +148,14 @@ def test_gptq_row_parallel_ignores_global_g_idx_without_desc_act():
         method = layer.quant_method
         import sglang_security_b200.layers.quantization.gptq as G
         calls = {}
-        orig = (G.repack_gptq, G.unpack_zeros)
+        orig = (G.repack_gptq, G.unpack_zeros, G.gemv_stream_repack)
         G.repack_gptq = lambda qw, perm: calls.setdefault("perm", perm) or qw
         G.unpack_zeros = lambda *a, **k_: None
+        G.gemv_stream_repack = lambda qw: None
         try:
             method.process_weights_after_loading(layer)
         finally:
-            G.repack_gptq, G.unpack_zeros = orig
+            G.repack_gptq, G.unpack_zeros, G.gemv_stream_repack = orig
         assert calls["perm"] is None and layer.b200_perm is None
     with pytest.raises(NotImplementedError):
         RowParallelLinear(k, n, bias=False, params_dtype=torch.float16,

@@ -16,8 +16,10 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 import torch
 
 from bench_gemm_decode import graph_time
-from sglang_security_b200.layers.quantization.w4a16_kernel import (awq_dequantize, unpack_zeros,
-                                                                  w4a16_gemm, w4a16_gemv_config)
+from sglang_security_b200.layers.quantization.w4a16_kernel import (awq_dequantize, gemv_stream_repack,
+                                                                  unpack_zeros, w4a16_gemm,
+                                                                  w4a16_gemv_config, w4a16_gemv_v2,
+                                                                  w4a16_gemv_v2_config)
 
 SHAPES = {"tp2": [(3584, 5120), (5120, 2560), (27648, 5120), (5120, 13824)],
           "tp4": [(1792, 5120), (5120, 1280), (13824, 5120), (5120, 6912)]}
@@ -28,6 +30,8 @@ def main():
     ap.add_argument("--tp", default="tp2,tp4")
     ap.add_argument("--ms", default="1,2,4,8,16,32,48,64,96,128,192,256,512,1024,2048")
     ap.add_argument("--splits", default="")
+    ap.add_argument("--splits2", default="", help="extra forced split-K factors for the stream GEMV")
+    ap.add_argument("--skip-ref", action="store_true")
     ap.add_argument("--dtype", default="float16")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bench_w4a16.json"))
     args = ap.parse_args()
@@ -42,7 +46,7 @@ def main():
                 qw = torch.randint(-2 ** 31, 2 ** 31 - 1, (k, n // 8), device=dev, dtype=torch.int64).to(torch.int32)
                 qz = torch.randint(-2 ** 31, 2 ** 31 - 1, (k // group, n // 8), device=dev, dtype=torch.int64).to(torch.int32)
                 sc = (torch.rand(k // group, n, device=dev) * 0.02).to(dt)
-                ws.append((qw, qz, unpack_zeros(qz, dt, True, False), sc))
+                ws.append((qw, qz, unpack_zeros(qz, dt, True, False), sc, gemv_stream_repack(qw)))
             reps = max(1, 32 // copies)
             for m in [int(v) for v in args.ms.split(",")]:
                 x = torch.randn(m, k, device=dev).to(dt)
@@ -59,13 +63,25 @@ def main():
                     t = graph_time(fns, reps)
                     res[name + "_us"] = round(t * 1e6, 2)
                 w4a16_gemv_config(-1, -1)
+                if m <= 16:
+                    for s in [0] + [int(v) for v in args.splits2.split(",") if v]:
+                        w4a16_gemv_v2_config(s)
+                        fns = [(lambda w=w: w4a16_gemv_v2(x, w[4], w[2], w[3], group)) for w in ws]
+                        t2 = graph_time(fns, reps)
+                        key = "gemv2" if s == 0 else f"gemv2_s{s}"
+                        res[key + "_us"] = round(t2 * 1e6, 2)
+                        if s == 0:
+                            res["gemv2_gbs"] = round(bytes_ / t2 / 1e9)
+                            res["gemv2_frac_hbm"] = round(bytes_ / t2 / 6548.5e9, 3)
+                    w4a16_gemv_v2_config(0)
                 fns = [(lambda w=w: w4a16_gemm(x, w[0], w[2], w[3], group)) for w in ws]
                 t = graph_time(fns, reps)
                 res["dispatch_us"] = round(t * 1e6, 2)
                 res["dispatch_gbs"] = round(bytes_ / t / 1e9)
                 res["dispatch_tflops"] = round(2.0 * m * n * k / t / 1e12, 1)
-                fns = [(lambda w=w: torch.matmul(x, awq_dequantize(w[0], w[3], w[1]))) for w in ws]
-                res["ref_dequant_matmul_us"] = round(graph_time(fns, reps) * 1e6, 2)
+                if not args.skip_ref:
+                    fns = [(lambda w=w: torch.matmul(x, awq_dequantize(w[0], w[3], w[1]))) for w in ws]
+                    res["ref_dequant_matmul_us"] = round(graph_time(fns, reps) * 1e6, 2)
                 print(json.dumps(res), flush=True)
                 rows.append(res)
             del ws
