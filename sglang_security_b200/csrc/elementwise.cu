@@ -18,6 +18,8 @@
 // produces (norm -> 16-bit -> quant) and differs from the CPU oracle only by reduction order.
 #include <cuda_fp8.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -535,8 +537,15 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
     ScopedKernelTimer timer("silu_and_mul", st);
     // cluster size: spread few rows over more SMs while every CTA keeps >= 256 vectors
     const int nvec = d / 8;
-    int S = M <= 4 ? 8 : M <= 16 ? 4 : M <= 32 ? 2 : 1;
-    while (S > 1 && nvec < S * kRowThreads) S >>= 1;
+    // (one CTA per row leaves a 14336-wide row — 56 exp + divide per thread — to 8 warps of one SM:
+    // 11.7 us at M = 64 in the whole-model launch list, profiles/r02_ncu_launches.json), so rows are
+    // split until about two CTAs per SM exist; B200_SILU_TARGET_CTAS overrides the target
+    static const int target = [] {
+      const char* e = std::getenv("B200_SILU_TARGET_CTAS");
+      return (e && *e) ? std::atoi(e) : 2 * device_sm_count();
+    }();
+    int S = 8;
+    while (S > 1 && (M * S > target || nvec < S * kRowThreads)) S >>= 1;
     const int per = ceil_div(ceil_div(nvec, S), 16) * 16;  // 128-groups stay inside one CTA
     if (dtype == B200_BF16)
       B200_CUDA_OK(launch_kernel(silu_mul_kernel<__nv_bfloat16>, dim3(M * S), dim3(kRowThreads), 0, st,

@@ -70,7 +70,9 @@ struct SmallMCfg {
   // registers).  The weight ring is as deep as shared memory allows — the kernel is bound by bytes
   // in flight (measured: 3/4/5 stages -> 3.2/4.4/5.7 TB/s) — while the activation ring, fed from
   // L2 and identical for every CTA, is only NX deep and lags the weight ring.
-  static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : 112 * 1024;
+  // MT = 64 keeps 12 KiB of headroom: at 112 KiB + barriers the second CTA of an SM did not fit
+  // (ncu showed 33 resident clusters of 4 for the MT = 64 instance = one CTA per SM)
+  static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : (MT == 64 ? 100 * 1024 : 112 * 1024);
   static constexpr int NX = (MT <= 32 && KS == 1) ? 3 : 2;
   static constexpr int NW = (BUDGET - NX * X_BYTES) / W_BYTES;
   static constexpr int NBUF = BLK ? (MT <= 64 ? 4 : 2) : 1;
@@ -412,8 +414,14 @@ int launch_smallm_ks(const void* x, int64_t ldx, const void* w, int64_t ldw, Sma
   if (S > num_kb) S = num_kb;
   p.kb_per_split = ceil_div(num_kb, S);
   p.pdl_late = pdl_late();
-  note_variant("fp8_smallm mt=%d blk=%d ar=%d ksub=%d splits=%d tiles=%d", MT, BLK ? 1 : 0,
-               AR ? 1 : 0, KSUB, S, n_tiles);
+  static int ctas_per_sm = -1;  // reported so that sweeps / tests can see the residency
+  if (ctas_per_sm < 0 &&
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kern, 192, C::SMEM_BYTES) != cudaSuccess) {
+    (void)cudaGetLastError();
+    ctas_per_sm = 0;
+  }
+  note_variant("fp8_smallm mt=%d blk=%d ar=%d ksub=%d splits=%d tiles=%d ctas_per_sm=%d", MT,
+               BLK ? 1 : 0, AR ? 1 : 0, KSUB, S, n_tiles, ctas_per_sm);
   {
     ScopedKernelTimer timer(timer_name, st);
     B200_CUDA_OK(launch_kernel(kern, dim3(n_tiles * S), dim3(192), C::SMEM_BYTES, st, S, pdl_family(p.M, kPdlGemmSmall), tw, tx, p));
