@@ -128,21 +128,21 @@ int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
                            size_t workspace_bytes, int num_splits, void* stream);
 
 /* Fused decode tail: same operands and math as b200_attn_decode / b200_attn_decode_fp8kv, but the
- * LAST CTA of every request to finish (ticket counter in `tickets`: uint32 [bs], zero before the
- * first call, self-resetting, so CUDA-graph replays need no memset) merges the split partials of
- * all heads itself — no b200_attn_merge launch — and, when q_out != NULL, also quantises the output
- * row per token to e4m3 exactly as b200_fp8_quant_per_token would from the rounded 16-bit row
- * (q_out [bs, q_out_stride] bytes, q_scales [bs] fp32): the o_proj input quantiser of
- * Fp8LinearMethod.apply (fp8_utils.py:454-648) disappears from the decode step.  write_o = 0 skips
- * the 16-bit output row when only q_out is consumed (ignored when num_splits == 1).
- * b200_attn_decode_fused_supported: 1 when Hq x num_splits fits the tail's shared memory.        */
+ * split partials are merged inside the kernel — the last split CTA of every (request, kv-head tile)
+ * to finish merges its own heads (ticket counters, no b200_attn_merge launch) — and, when
+ * q_out != NULL, the last tile of a request also quantises the output row per token to e4m3 exactly
+ * as b200_fp8_quant_per_token would from the rounded 16-bit row (q_out [bs, q_out_stride] bytes,
+ * q_scales [bs] fp32): the o_proj input quantiser of Fp8LinearMethod.apply (fp8_utils.py:454-648)
+ * disappears from the decode step.  `tickets`: b200_attn_decode_fused_ticket_bytes(bs, Hq, Hkv) bytes
+ * of device memory, zero before the first call; the counters re-arm themselves, so CUDA-graph
+ * replays need no memset.  Requires num_splits > 1 or q_out != NULL.                             */
 int b200_attn_decode_fused(const void* q, int64_t q_stride, const void* k_cache,
                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
                            const int32_t* req_to_token, int64_t req_to_token_stride,
                            const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
                            int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
                            void* workspace, size_t workspace_bytes, int num_splits, void* tickets,
-                           void* q_out, int64_t q_out_stride, float* q_scales, int write_o,
+                           size_t ticket_bytes, void* q_out, int64_t q_out_stride, float* q_scales,
                            void* stream);
 int b200_attn_decode_fp8kv_fused(const void* q, int64_t q_stride, const void* k_cache,
                                  const void* v_cache, int64_t kv_row_stride, void* o,
@@ -151,9 +151,9 @@ int b200_attn_decode_fp8kv_fused(const void* q, int64_t q_stride, const void* k_
                                  const int64_t* seq_lens, int bs, int Hq, int Hkv, int D, int Dv,
                                  float scale, float logit_cap, float k_scale, float v_scale,
                                  int dtype, void* workspace, size_t workspace_bytes, int num_splits,
-                                 void* tickets, void* q_out, int64_t q_out_stride, float* q_scales,
-                                 int write_o, void* stream);
-int b200_attn_decode_fused_supported(int Hq, int D, int num_splits, int fp8kv);
+                                 void* tickets, size_t ticket_bytes, void* q_out,
+                                 int64_t q_out_stride, float* q_scales, void* stream);
+size_t b200_attn_decode_fused_ticket_bytes(int bs, int Hq, int Hkv);
 
 /* Merge of split-KV partial states (replaces _fwd_kernel_stage2, decode_attention.py:497-557,
  * and merge_state_v2, sgl-kernel/csrc/attention/merge_attn_states.cu): exposed for tests.
@@ -250,6 +250,15 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
                            int64_t as_row_stride, int64_t as_col_stride, const float* bs,
                            int64_t bs_row_stride, const void* bias, void* out, int64_t ldc, int M,
                            int N, int K, int out_dtype, void* stream);
+
+/* ---- dense 16-bit GEMM (unquantised layers, lm_head) ------------------------------------------ */
+/* out[M,N] = x[M,K] . w[N,K]^T (+ bias[N]); bf16 / f16 operands and output, fp32 accumulation on
+ * tcgen05 (same persistent TMA kernel as the FP8 path, kind::f16).  Replaces F.linear in
+ * UnquantizedLinearMethod.apply (python/sglang/srt/layers/linear.py:170-176) and the lm_head matmul of
+ * LogitsProcessor._get_logits (layers/logits_processor.py:425-455).  x / w 16-byte aligned, row
+ * strides (in elements) multiples of 8.                                                         */
+int b200_gemm_16bit(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
+                    void* out, int64_t ldc, int M, int N, int K, int dtype, void* stream);
 
 /* ---- INT4 weight-only (W4A16): AWQ / GPTQ ------------------------------------- */
 /* Bit-exact AWQ dequant with the reference layouts (replaces sgl_kernel.awq_dequantize,

@@ -60,14 +60,14 @@ _SIGNATURES = {
     "b200_attn_decode_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_int, c_int, c_float, c_float, c_int, c_void_p,
-                                       c_size_t, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_int,
-                                       c_void_p]),
+                                       c_size_t, c_int, c_void_p, c_size_t, c_void_p, c_int64,
+                                       c_void_p, c_void_p]),
     "b200_attn_decode_fp8kv_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
                                              c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int,
                                              c_int, c_int, c_int, c_int, c_float, c_float, c_float,
                                              c_float, c_int, c_void_p, c_size_t, c_int, c_void_p,
-                                             c_void_p, c_int64, c_void_p, c_int, c_void_p]),
-    "b200_attn_decode_fused_supported": (c_int, [c_int, c_int, c_int, c_int]),
+                                             c_size_t, c_void_p, c_int64, c_void_p, c_void_p]),
+    "b200_attn_decode_fused_ticket_bytes": (c_size_t, [c_int, c_int, c_int]),
     "b200_attn_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int,
                                 c_int, c_int, c_int, c_int, c_void_p]),
     "b200_attn_extend": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_int64,
@@ -103,6 +103,8 @@ _SIGNATURES = {
     "b200_fp8_gemm_block128_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                           c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
                                           c_int64, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_gemm_16bit": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
+                                c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv_config": (c_int, [c_int, c_int]),

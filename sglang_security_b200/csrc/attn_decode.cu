@@ -46,14 +46,13 @@ struct DecodeParams {
   float logit_cap;  // <= 0: disabled
   float v_scale;    // FP8 KV pool only: output multiplier (k_scale is folded into qk_scale)
   int pdl_late;
-  // Fused tail (b200_attn_decode*_fused): the LAST CTA of a request to finish (ticket counter)
-  // merges the split partials of all its heads and, optionally, quantises the output row to e4m3
-  // per token — the merge kernel and the o_proj input quantiser disappear from the step.
-  unsigned* tickets;     // [bs], zero before the first launch, self-resetting; null = no tail
+  // Fused tail (b200_attn_decode*_fused, see decode_fused_tail): split partials are merged and,
+  // optionally, the output row is quantised to e4m3 per token inside this kernel — the merge kernel
+  // and the o_proj input quantiser disappear from the step.
+  unsigned* tickets;     // [bs * (1 + gridDim.y)], zero before the first launch, self-resetting
   uint8_t* q_out;        // [bs, q_out_stride] e4m3 or null
   int64_t q_out_stride;
   float* q_scales;       // [bs]
-  int write_o;           // 0: the 16-bit output row is not needed (only q_out is consumed)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -144,20 +143,18 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
 }
 
 
-// ---- fused tail: merge of the split partials (+ per-token FP8 quantisation) by the last CTA --------
-// Every CTA of request b that has work publishes its partials, fences and takes a ticket; the one
-// that draws the last ticket (nvalid splits x gridDim.y CTAs) sees all partials of the request
-// (threadFenceReduction pattern) and finishes the row: same arithmetic as attn_merge_kernel
-// (num * 1/den, one rounding to T) followed by fp8_quant_per_token_kernel's (scale = amax / 448,
-// q = sat(x * (1/scale)) on the ROUNDED 16-bit values), so the bytes equal merge + quantiser.
-// Shared memory (the idle pipeline ring): weights [Hq][num_splits] + 1/den [Hq] fp32, then the row as T.
-__host__ __device__ inline size_t decode_tail_wgt_bytes(int Hq, int num_splits) {
-  return (static_cast<size_t>(Hq) * (num_splits + 1) * 4 + 15) & ~static_cast<size_t>(15);
-}
-__host__ __device__ inline size_t decode_tail_smem_bytes(int Hq, int D, int num_splits) {
-  return decode_tail_wgt_bytes(Hq, num_splits) + static_cast<size_t>(Hq) * D * 2;
-}
-
+// ---- fused tail: merge of the split partials (+ per-token FP8 quantisation) inside the kernel ----
+// Two levels of ticket counters (threadFenceReduction pattern; bar.sync + one gpu-scope acq_rel
+// atomic by thread 0 orders the CTA's stores before the draw and the winner's loads after it):
+//   level 1, one counter per (request, kv-head tile): the LAST of the nvalid split CTAs of that tile
+//            merges the partials of its own query heads — same arithmetic as attn_merge_kernel
+//            (num * 1/den, one rounding to T) — and writes them to the 16-bit output row;
+//   level 2, one counter per request (only when q_out is requested): the last tile to finish
+//            quantises the whole row exactly as fp8_quant_per_token_kernel would (scale = amax / 448,
+//            q = sat(x * (1/scale)) on the rounded 16-bit values).
+// The merge work is spread over all (request, tile) pairs instead of one CTA per request; counters
+// re-arm themselves, so CUDA-graph replays need no memset.
+// Ticket words: [0, bs) level 2, bs + b * gridDim.y + blockIdx.y level 1.
 struct TailDev {
   unsigned* tickets;
   uint8_t* q_out;
@@ -167,7 +164,7 @@ struct TailDev {
   int64_t o_stride;
   const float* part_o;
   const float* part_lse;
-  int Hq, num_splits, write_o;
+  int Hq, num_splits, bs;
 };
 __device__ __forceinline__ TailDev tail_of(const DecodeParams& p) {
   TailDev t;
@@ -181,90 +178,73 @@ __device__ __forceinline__ TailDev tail_of(const DecodeParams& p) {
   t.part_lse = p.part_lse;
   t.Hq = p.Hq;
   t.num_splits = p.num_splits;
-  t.write_o = p.write_o;
+  t.bs = p.bs;
   return t;
 }
 
-template <typename T, int THREADS>
-__device__ __noinline__ void decode_fused_tail(const TailDev p, int b, int nvalid, int D,
-                                               uint8_t* smem) {
-  __shared__ unsigned s_last;
-  __shared__ float s_red[THREADS / 32];
-  // bar.sync orders every thread's partial / output stores before thread 0's gpu-scope acq_rel
-  // ticket draw (release is cumulative over what the barrier made visible to thread 0); on the
-  // last CTA the same draw is the acquire, and the second barrier hands it to the other threads.
-  __syncthreads();   // also: the pipeline ring is idle from here on
+// true on every thread of the CTA that drew the last of `total` tickets (and re-arms the counter)
+__device__ __forceinline__ bool draw_last_ticket(unsigned* ticket, unsigned total, unsigned* s_flag) {
+  __syncthreads();  // every thread's stores are ordered before thread 0's release
   if (threadIdx.x == 0) {
-    const unsigned total = static_cast<unsigned>(nvalid) * gridDim.y;
     unsigned prev;
     asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;\n"
-                 : "=r"(prev) : "l"(p.tickets + b) : "memory");
+                 : "=r"(prev) : "l"(ticket) : "memory");
     const bool last = prev + 1 == total;
-    if (last) p.tickets[b] = 0u;  // every other CTA of this request has drawn: safe to re-arm
-    s_last = last ? 1u : 0u;
+    if (last) *ticket = 0u;  // every other participant has drawn: safe to re-arm
+    *s_flag = last ? 1u : 0u;
   }
   __syncthreads();
-  if (!s_last) return;
-  const int Hq = p.Hq, NS = p.num_splits;
-  const int n4 = Hq * D / 4;
-  float* wgt = reinterpret_cast<float*>(smem);             // [Hq][NS] unnormalised weights
-  float* inv_den = wgt + Hq * NS;                           // [Hq]
-  T* row = reinterpret_cast<T*>(smem + decode_tail_wgt_bytes(Hq, NS));
-  if (NS > 1) {
-    for (int h = threadIdx.x; h < Hq; h += THREADS) {
-      const float* lse = p.part_lse + (static_cast<int64_t>(b) * Hq + h) * NS;
-      float M = -INFINITY;
-      for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldcg(lse + s));
-      float den = 0.f;
-      for (int s = 0; s < nvalid; ++s) {
-        const float f = fast_exp2(__ldcg(lse + s) - M);
-        wgt[h * NS + s] = f;
-        den += f;
-      }
-      inv_den[h] = 1.f / den;
-    }
-    __syncthreads();
-  }
+  return *s_flag != 0u;
+}
+
+template <typename T, int THREADS>
+__device__ __noinline__ void decode_fused_tail(const TailDev p, int b, int hq0, int heads_here,
+                                               int nvalid, int D) {
+  __shared__ unsigned s_flag;
+  __shared__ float s_red[THREADS / 32];
+  const int NS = p.num_splits;
   T* orow = static_cast<T*>(p.o) + static_cast<int64_t>(b) * p.o_stride;
-  float amax = 0.f;
-  for (int it = threadIdx.x; it < n4; it += THREADS) {
-    const int e0 = it * 4, h = e0 / D, d = e0 - h * D;
-    float v[4];
-    if (NS > 1) {
-      const float* po = p.part_o + (static_cast<int64_t>(b) * Hq + h) * NS * D + d;
-      float num[4] = {0.f, 0.f, 0.f, 0.f};
+  if (NS > 1) {
+    if (!draw_last_ticket(p.tickets + p.bs + b * gridDim.y + blockIdx.y,
+                          static_cast<unsigned>(nvalid), &s_flag))
+      return;
+    for (int it = threadIdx.x; it < heads_here * D / 4; it += THREADS) {
+      const int e0 = it * 4, h = e0 / D, d = e0 - h * D;
+      const int hq = hq0 + h;
+      const int64_t base = (static_cast<int64_t>(b) * p.Hq + hq) * NS;
+      float M = -INFINITY;
+      for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldcg(p.part_lse + base + s));
+      float den = 0.f, num[4] = {0.f, 0.f, 0.f, 0.f};
       for (int s = 0; s < nvalid; ++s) {
-        const float w = wgt[h * NS + s];
-        const float4 x = __ldcg(reinterpret_cast<const float4*>(po + s * D));
+        const float w = fast_exp2(__ldcg(p.part_lse + base + s) - M);
+        const float4 x = __ldcg(reinterpret_cast<const float4*>(p.part_o + (base + s) * D + d));
+        den += w;
         num[0] += w * x.x;
         num[1] += w * x.y;
         num[2] += w * x.z;
         num[3] += w * x.w;
       }
-      const float inv = inv_den[h];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) v[e] = to_float<T>(from_float<T>(num[e] * inv));
-      if (p.write_o) {
-        uint2 pk;
-        pk.x = pack2<T>(v[0], v[1]);
-        pk.y = pack2<T>(v[2], v[3]);
-        *reinterpret_cast<uint2*>(orow + e0) = pk;
-      }
-    } else {
-      const uint2 pk = __ldcg(reinterpret_cast<const uint2*>(orow + e0));
-      const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
-      v[0] = a.x; v[1] = a.y; v[2] = c.x; v[3] = c.y;
-    }
-    if (p.q_out) {
+      const float inv = 1.f / den;
       uint2 pk;
-      pk.x = pack2<T>(v[0], v[1]);
-      pk.y = pack2<T>(v[2], v[3]);
-      *reinterpret_cast<uint2*>(row + e0) = pk;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) amax = fmaxf(amax, fabsf(v[e]));
+      pk.x = pack2<T>(num[0] * inv, num[1] * inv);
+      pk.y = pack2<T>(num[2] * inv, num[3] * inv);
+      *reinterpret_cast<uint2*>(orow + hq * D + d) = pk;
     }
   }
   if (!p.q_out) return;
+  if (!draw_last_ticket(p.tickets + b, gridDim.y, &s_flag)) return;
+  // the whole 16-bit row of request b is final: per-token quantisation (two passes over 8 KiB of L2)
+  const int n8 = p.Hq * D / 8;
+  float amax = 0.f;
+  for (int it = threadIdx.x; it < n8; it += THREADS) {
+    const uint4 pk = __ldcg(reinterpret_cast<const uint4*>(orow) + it);
+    const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 v = unpack2<T>(w[e]);
+      amax = fmaxf(amax, fmaxf(fabsf(v.x), fabsf(v.y)));
+    }
+  }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = amax;
@@ -276,19 +256,20 @@ __device__ __noinline__ void decode_fused_tail(const TailDev p, int b, int nvali
   if (threadIdx.x == 0) p.q_scales[b] = scale;
   const float inv = scale > 0.f ? 1.0f / scale : 0.f;
   uint8_t* qrow = p.q_out + static_cast<int64_t>(b) * p.q_out_stride;
-  for (int it = threadIdx.x; it < n4; it += THREADS) {
-    const uint2 pk = *reinterpret_cast<const uint2*>(row + it * 4);
-    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
-    const float v[4] = {a.x, a.y, c.x, c.y};
-    uint32_t q = 0;
+  for (int it = threadIdx.x; it < n8; it += THREADS) {
+    const uint4 pk = __ldcg(reinterpret_cast<const uint4*>(orow) + it);
+    const uint32_t w[4] = {pk.x, pk.y, pk.z, pk.w};
+    uint32_t q[2] = {0u, 0u};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const float x = fmaxf(fminf(v[e] * inv, 448.0f), -448.0f);
+      const float2 v = unpack2<T>(w[e]);
+      const float x0 = fmaxf(fminf(v.x * inv, 448.0f), -448.0f);
+      const float x1 = fmaxf(fminf(v.y * inv, 448.0f), -448.0f);
       uint16_t r;
-      asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(x));
-      q |= static_cast<uint32_t>(r & 0xffu) << (8 * e);
+      asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(x1), "f"(x0));
+      q[e >> 1] |= static_cast<uint32_t>(r) << (16 * (e & 1));
     }
-    *reinterpret_cast<uint32_t*>(qrow + it * 4) = q;
+    *reinterpret_cast<uint2*>(qrow + it * 8) = make_uint2(q[0], q[1]);
   }
 }
 
@@ -570,7 +551,8 @@ attn_decode_mma_kernel(const DecodeParams p) {
       if (d == 0) p.part_lse[pidx] = M + log2f(den);
     }
   }
-  if constexpr (TAIL) decode_fused_tail<T, NW * 32>(tail_of(p), b, ceil_div(len, chunk), D, smem);
+  if constexpr (TAIL)
+    decode_fused_tail<T, NW * 32>(tail_of(p), b, kvh * p.group + head0, heads_here, ceil_div(len, chunk), D);
 }
 
 // Merge of split partials: one CTA per (query head, request).
@@ -728,38 +710,33 @@ static int dispatch_decode_fp8kv(const DecodeParams& p, int D, int G, cudaStream
 // Host side of the fused tail (see decode_fused_tail).
 struct DecodeTail {
   void* tickets;
+  size_t ticket_bytes;
   void* q_out;
   int64_t q_out_stride;
   float* q_scales;
-  int write_o;
 };
 
-static int apply_tail(DecodeParams& p, const DecodeTail* tail, int D, size_t ring_bytes,
-                      const char* who) {
+static int apply_tail(DecodeParams& p, const DecodeTail* tail, int D, const char* who) {
   p.tickets = nullptr;
   p.q_out = nullptr;
   p.q_out_stride = 0;
   p.q_scales = nullptr;
-  p.write_o = 1;
   if (!tail) return 0;
-  B200_REQUIRE(tail->tickets, "%s: null ticket buffer", who);
+  const size_t need = static_cast<size_t>(p.bs) * (1 + p.Hkv * p.head_tiles) * sizeof(unsigned);
+  B200_REQUIRE(tail->tickets && tail->ticket_bytes >= need,
+               "%s: ticket buffer too small (%zu < %zu bytes)", who, tail->ticket_bytes, need);
   B200_REQUIRE((tail->q_out == nullptr) == (tail->q_scales == nullptr),
                "%s: q_out and q_scales go together", who);
-  B200_REQUIRE(tail->q_out || tail->write_o, "%s: nothing to produce (no q_out, write_o = 0)", who);
-  B200_REQUIRE(!tail->q_out || (tail->q_out_stride % 4 == 0 &&
-                                (reinterpret_cast<uintptr_t>(tail->q_out) & 3u) == 0),
-               "%s: q_out must be 4-byte aligned with q_out_stride %% 4 == 0", who);
-  B200_REQUIRE(p.o_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(p.o) & 7u) == 0,
-               "%s: o must be 8-byte aligned with o_stride %% 4 == 0", who);
-  B200_REQUIRE(decode_tail_smem_bytes(p.Hq, D, p.num_splits) <= ring_bytes,
-               "%s: Hq=%d x num_splits=%d does not fit the tail's shared memory "
-               "(use b200_attn_decode_fused_supported)", who, p.Hq, p.num_splits);
+  B200_REQUIRE(tail->q_out || p.num_splits > 1, "%s: nothing to fuse (one split, no q_out)", who);
+  B200_REQUIRE(!tail->q_out || (tail->q_out_stride % 8 == 0 &&
+                                (reinterpret_cast<uintptr_t>(tail->q_out) & 7u) == 0),
+               "%s: q_out must be 8-byte aligned with q_out_stride %% 8 == 0", who);
+  B200_REQUIRE(p.o_stride % 8 == 0 && aligned16(p.o) && (p.Hq * D) % 8 == 0,
+               "%s: o must be 16-byte aligned with o_stride %% 8 == 0", who);
   p.tickets = static_cast<unsigned*>(tail->tickets);
   p.q_out = static_cast<uint8_t*>(tail->q_out);
   p.q_out_stride = tail->q_out_stride;
   p.q_scales = tail->q_scales;
-  // with one split the CTAs write the 16-bit row themselves and the tail reads it back
-  p.write_o = (tail->write_o || p.num_splits == 1) ? 1 : 0;
   return 0;
 }
 
@@ -855,9 +832,7 @@ static int attn_decode_impl(const void* q, int64_t q_stride, const void* k_cache
   p.part_o = static_cast<float*>(workspace);
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
 
-  if (int rc = apply_tail(p, tail, D, /*ring_bytes=*/MmaCfg<128, kNT, kStages, kNW>::SMEM_BYTES * D / 128,
-                          "b200_attn_decode_fused"))
-    return rc;
+  if (int rc = apply_tail(p, tail, D, "b200_attn_decode_fused")) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = dtype == B200_BF16 ? dispatch_decode<__nv_bfloat16>(p, D, G, st)
                               : dispatch_decode<__half>(p, D, G, st);
@@ -885,20 +860,19 @@ int b200_attn_decode_fused(const void* q, int64_t q_stride, const void* k_cache,
                            const int64_t* req_pool_indices, const int64_t* seq_lens, int bs, int Hq,
                            int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
                            void* workspace, size_t workspace_bytes, int num_splits, void* tickets,
-                           void* q_out, int64_t q_out_stride, float* q_scales, int write_o,
+                           size_t ticket_bytes, void* q_out, int64_t q_out_stride, float* q_scales,
                            void* stream) {
-  b200::DecodeTail tail = {tickets, q_out, q_out_stride, q_scales, write_o};
+  b200::DecodeTail tail = {tickets, ticket_bytes, q_out, q_out_stride, q_scales};
   return attn_decode_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride, req_to_token,
                           req_to_token_stride, req_pool_indices, seq_lens, bs, Hq, Hkv, D, Dv, scale,
                           logit_cap, dtype, workspace, workspace_bytes, num_splits, stream, &tail);
 }
 
-int b200_attn_decode_fused_supported(int Hq, int D, int num_splits, int fp8kv) {
+size_t b200_attn_decode_fused_ticket_bytes(int bs, int Hq, int Hkv) {
   using namespace b200;
-  if (D != 64 && D != 128) return 0;
-  const size_t ring = fp8kv ? Fp8KvCfg<128, kNT8, 2, kNW>::SMEM_BYTES * static_cast<size_t>(D) / 128
-                            : MmaCfg<128, kNT, kStages, kNW>::SMEM_BYTES * static_cast<size_t>(D) / 128;
-  return decode_tail_smem_bytes(Hq, D, num_splits) <= ring ? 1 : 0;
+  if (bs <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return 0;
+  const int group = Hq / Hkv;
+  return static_cast<size_t>(bs) * (1 + Hkv * ceil_div(group, tile_heads(group))) * sizeof(unsigned);
 }
 
 int b200_attn_decode_fp8kv_split_align(void) { return b200::decode_align_fp8kv(); }
@@ -956,9 +930,7 @@ static int attn_decode_fp8kv_impl(const void* q, int64_t q_stride, const void* k
   { static const char* e = std::getenv("B200_PDL_LATE"); p.pdl_late = e ? std::atoi(e) : 1; }
   p.part_o = static_cast<float*>(workspace);
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
-  if (int rc = apply_tail(p, tail, D, /*ring_bytes=*/Fp8KvCfg<128, kNT8, 2, kNW>::SMEM_BYTES * D / 128,
-                          "b200_attn_decode_fp8kv_fused"))
-    return rc;
+  if (int rc = apply_tail(p, tail, D, "b200_attn_decode_fp8kv_fused")) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, st)
                                     : dispatch_decode_fp8kv<__half>(p, D, G, st);
@@ -989,9 +961,9 @@ int b200_attn_decode_fp8kv_fused(const void* q, int64_t q_stride, const void* k_
                                  const int64_t* seq_lens, int bs, int Hq, int Hkv, int D, int Dv,
                                  float scale, float logit_cap, float k_scale, float v_scale,
                                  int dtype, void* workspace, size_t workspace_bytes, int num_splits,
-                                 void* tickets, void* q_out, int64_t q_out_stride, float* q_scales,
-                                 int write_o, void* stream) {
-  b200::DecodeTail tail = {tickets, q_out, q_out_stride, q_scales, write_o};
+                                 void* tickets, size_t ticket_bytes, void* q_out,
+                                 int64_t q_out_stride, float* q_scales, void* stream) {
+  b200::DecodeTail tail = {tickets, ticket_bytes, q_out, q_out_stride, q_scales};
   return attn_decode_fp8kv_impl(q, q_stride, k_cache, v_cache, kv_row_stride, o, o_stride,
                                 req_to_token, req_to_token_stride, req_pool_indices, seq_lens, bs, Hq,
                                 Hkv, D, Dv, scale, logit_cap, k_scale, v_scale, dtype, workspace,

@@ -366,7 +366,8 @@ attn_decode_fp8kv_kernel(const DecodeParams p) {
       if (d == 0) p.part_lse[pidx] = M + log2f(den);
     }
   }
-  if constexpr (TAIL) decode_fused_tail<T, NW * 32>(tail_of(p), b, ceil_div(len, chunk), D, smem);
+  if constexpr (TAIL)
+    decode_fused_tail<T, NW * 32>(tail_of(p), b, kvh * p.group + head0, heads_here, ceil_div(len, chunk), D);
 }
 
 }  // namespace b200

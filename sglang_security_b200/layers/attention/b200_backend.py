@@ -76,14 +76,17 @@ class B200AttnBackend(AttentionBackend):
         self._graph_max_bs = 0
         # fused decode tail (merge + optional o_proj input quantisation by the last CTA of a request)
         self.fused_tail = os.environ.get("B200_ATTN_FUSED_TAIL", "1") != "0"
-        self._tickets = torch.zeros(4096, dtype=torch.int32, device=self.device)
+        self._tickets = torch.zeros(256 * (1 + self.num_head), dtype=torch.int32, device=self.device)
 
     def _ticket_buffer(self, bs: int) -> torch.Tensor:
-        if self._tickets.numel() < bs:
+        """Zero-initialised, self-re-arming counters of the fused tail (one per request and one per
+        (request, kv-head tile)); bs * (1 + num_head) words always cover the kernel's need."""
+        need = bs * (1 + self.num_head)
+        if self._tickets.numel() < need:
             if torch.cuda.is_current_stream_capturing():
                 raise _lib.B200Error("B200AttnBackend: ticket buffer too small during graph capture "
                                      "(call init_cuda_graph_state with the largest batch first)")
-            self._tickets = torch.zeros(max(bs, 2 * self._tickets.numel()), dtype=torch.int32,
+            self._tickets = torch.zeros(max(need, 2 * self._tickets.numel()), dtype=torch.int32,
                                         device=self.device)
         return self._tickets
 
@@ -265,17 +268,16 @@ class B200AttnBackend(AttentionBackend):
         common = common + (_lib.dtype_code(q.dtype), _lib.ptr(ws), 0 if ws is None else ws.numel(),
                            md.num_splits)
         # the tail only pays when it replaces a launch: the merge (splits > 1) or the quantiser
-        fused = (self.fused_tail and (md.num_splits > 1 or fp8_out) and
-                 self.lib.b200_attn_decode_fused_supported(hq, dv, md.num_splits, 1 if fp8kv else 0))
+        fused = self.fused_tail and (md.num_splits > 1 or fp8_out) and (hq * dv) % 8 == 0
         if fused:
             qa = sa = None
             if fp8_out:
                 qa = torch.empty((bs, hq * dv), dtype=torch.float8_e4m3fn, device=q.device)
                 sa = torch.empty((bs, 1), dtype=torch.float32, device=q.device)
             fn = self.lib.b200_attn_decode_fp8kv_fused if fp8kv else self.lib.b200_attn_decode_fused
-            rc = fn(*common, self._ticket_buffer(bs).data_ptr(), _lib.ptr(qa),
-                    0 if qa is None else qa.stride(0), _lib.ptr(sa), 0 if fp8_out else 1,
-                    _lib.current_stream())
+            tickets = self._ticket_buffer(bs)
+            rc = fn(*common, tickets.data_ptr(), tickets.numel() * 4, _lib.ptr(qa),
+                    0 if qa is None else qa.stride(0), _lib.ptr(sa), _lib.current_stream())
             _lib.check(rc, "b200_attn_decode_fused")
             if fp8_out:
                 from ..quantization.fp8_utils import QuantizedActivation

@@ -16,6 +16,7 @@ from ..distributed.parallel_state import (get_tensor_model_parallel_rank,
                                           get_tp_custom_all_reduce,
                                           tensor_model_parallel_all_gather,
                                           tensor_model_parallel_all_reduce)
+from .dense_kernel import dense_supported, gemm_16bit
 from .quantization.base_config import LinearMethodBase, QuantizationConfig, set_weight_attrs
 
 
@@ -26,8 +27,9 @@ def divide(a: int, b: int) -> int:
 
 
 class UnquantizedLinearMethod(LinearMethodBase):
-    """16-bit weights: plain library GEMM (cuBLAS through torch), as in the reference
-    (linear.py:143-176).  Not part of the quantised hot path."""
+    """16-bit weights (linear.py:143-176).  CUDA bf16/f16 operands run on the in-tree tcgen05 dense
+    GEMM (csrc/dense_gemm.cu); anything else (the CPU tensors of the gloo host-logic tests, fp32)
+    is torch's F.linear exactly as in the reference."""
 
     def create_weights(self, layer, input_size_per_partition, output_partition_sizes, input_size,
                        output_size, params_dtype, **extra_weight_attrs):
@@ -39,6 +41,8 @@ class UnquantizedLinearMethod(LinearMethodBase):
         set_weight_attrs(weight, extra_weight_attrs)
 
     def apply(self, layer, x, bias=None):
+        if dense_supported(x, layer.weight):
+            return gemm_16bit(x, layer.weight, bias)
         return F.linear(x, layer.weight, bias)
 
 

@@ -18,6 +18,7 @@ per-step work (slot allocation, req_to_token writes) is done by the caller.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from types import SimpleNamespace
 from typing import Optional
@@ -28,11 +29,14 @@ import torch.nn.functional as F
 from ..distributed.parallel_state import (tensor_model_parallel_all_gather,
                                           tensor_model_parallel_all_reduce)
 from ..layers.attention.b200_backend import B200AttnBackend
+from ..layers.dense_kernel import gemm_16bit
 from ..layers.layernorm import RMSNorm
 from ..layers.rotary_embedding import RotaryEmbedding
 from ..mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
 from .decoder_layer import B200DecoderLayer
 from .forward_batch_info import ForwardBatch, ForwardMode
+
+_LM_HEAD_LIBRARY = os.environ.get("B200_LM_HEAD_LIBRARY", "0") == "1"
 
 FP8 = torch.float8_e4m3fn
 
@@ -196,7 +200,8 @@ class B200DecodeStep:
         for L in self.layers:
             h, residual = L(positions, h, forward_batch, residual)
         h, _ = self.final_norm(h, residual)
-        logits = F.linear(h, self.lm_head)
+        # in-tree tcgen05 dense GEMM (B200_LM_HEAD_LIBRARY=1: the library matmul, for A/B runs only)
+        logits = F.linear(h, self.lm_head) if _LM_HEAD_LIBRARY else gemm_16bit(h, self.lm_head)
         if self.tp_size > 1:
             logits = tensor_model_parallel_all_gather(logits)
         out_token_ids.copy_(logits.argmax(-1))

@@ -249,11 +249,10 @@ def test_decode_fused_tail_full_batch_against_oracle():
     assert st["max_abs"] <= MAX_ABS and st["rel_l2"] <= REL_L2, st
 
 
-def test_decode_fused_tail_unsupported_shape_falls_back():
+def test_decode_fused_tail_ticket_sizing():
     from sglang_security_b200 import _lib
 
     lib = _lib.load()
-    assert lib.b200_attn_decode_fused_supported(32, 128, 2, 0) == 1
-    assert lib.b200_attn_decode_fused_supported(32, 128, 2, 1) == 1
-    assert lib.b200_attn_decode_fused_supported(128, 128, 64, 0) == 0   # weights + row > ring
-    assert lib.b200_attn_decode_fused_supported(32, 96, 2, 0) == 0
+    assert lib.b200_attn_decode_fused_ticket_bytes(64, 32, 8) == 64 * (1 + 8) * 4
+    assert lib.b200_attn_decode_fused_ticket_bytes(3, 40, 2) == 3 * (1 + 2 * 2) * 4   # group 20: two head tiles
+    assert lib.b200_attn_decode_fused_ticket_bytes(1, 7, 2) == 0

@@ -169,8 +169,6 @@ def test_extend_fp8kv_matches_oracle(hq, hkv, d, scales):
     pool.k_buffer[0].copy_(init_k)
     pool.v_buffer[0].copy_(init_v)
     backend = B200AttnBackend(mr)
-    if fused_tail is not None:
-        backend.fused_tail = fused_tail
     t = case.q.shape[0]
     qkv = torch.cat([case.q, case.k_new.reshape(t, -1), case.v_new.reshape(t, -1)], dim=1).cuda()
     q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
