@@ -70,10 +70,13 @@ struct SmallMCfg {
   // registers).  The weight ring is as deep as shared memory allows — the kernel is bound by bytes
   // in flight (measured: 3/4/5 stages -> 3.2/4.4/5.7 TB/s) — while the activation ring, fed from
   // L2 and identical for every CTA, is only NX deep and lags the weight ring.
-  // MT = 64 keeps 12 KiB of headroom: at 112 KiB + barriers the second CTA of an SM did not fit
-  // (ncu showed 33 resident clusters of 4 for the MT = 64 instance = one CTA per SM)
-  static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : (MT == 64 ? 100 * 1024 : 112 * 1024);
-  static constexpr int NX = (MT <= 32 && KS == 1) ? 3 : 2;
+  // MT = 64: 5 weight + 3 activation slots = 104 KiB, the footprint of the MT <= 32 instances that
+  // are known to run two CTAs per SM (ncu showed one CTA per SM for the 112 KiB ring)
+  static constexpr int BUDGET = (BLK && MT == 128) ? 208 * 1024 : (MT == 64 ? 108 * 1024 : 112 * 1024);
+  // MT = 64: three activation slots like the smaller instances.  With two, the x tile of block i is only requested when the
+  // MMA of block i - 2 retires, so every other K block exposed an L2 round trip (measured: the same
+  // 25 MB weight took 9.4 us at MT = 32 and 14-16 us at MT = 64, profiles/r02_bench_gemm_midm_mt64.json)
+  static constexpr int NX = (MT <= 32 && KS == 1) ? 3 : (MT == 64 ? 3 : 2);
   static constexpr int NW = (BUDGET - NX * X_BYTES) / W_BYTES;
   static constexpr int NBUF = BLK ? (MT <= 64 ? 4 : 2) : 1;
   static constexpr int TCOLS = (NBUF * MT) < 32 ? 32 : NBUF * MT;

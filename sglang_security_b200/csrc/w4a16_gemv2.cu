@@ -137,8 +137,10 @@ __device__ __forceinline__ uint32_t g2_hmul2(uint32_t a, uint32_t b) {
   return r;
 }
 
-// MT = number of 8-token tiles (1: M <= 8, 2: M <= 16)
-template <typename T, int MT>
+// MT = number of 8-token tiles (1: M <= 8, 2: M <= 16).  SPG = 32-k steps per quantisation group
+// known at compile time (1, 2, 4 = groups of 32, 64, 128: the fold sits at fixed places of the
+// unrolled round, no counters) or 0 = any other group size (run-time step counter).
+template <typename T, int MT, int SPG>
 __global__ void __launch_bounds__(kG2Threads, MT == 1 ? 3 : 2)
 w4a16_gemv2_kernel(const Gemv2Params p) {
   using MG = G2Magic<T>;
@@ -172,32 +174,42 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
     const T* zr = static_cast<const T*>(p.zeros);
     float* szf = reinterpret_cast<float*>(smem + p.sz_off);
     const int n0 = n_grp * 128;
-    for (int id = threadIdx.x; id < ng * 256; id += kG2Threads) {
-      const int gi = id >> 8, which = (id >> 7) & 1, c = id & 127;
-      const int n = n0 + c;
-      float v = 0.f;
-      if (n < p.N) {
-        const int64_t off = static_cast<int64_t>(grp_lo + gi) * p.N + n;
-        v = which ? to_float<T>(__ldg(zr + off)) - MG::kMagic : to_float<T>(__ldg(sc + off));
+    for (int id = threadIdx.x; id < ng * 32; id += kG2Threads) {  // 8 columns per item
+      const int gi = id >> 5, which = (id >> 4) & 1, c8 = (id & 15) * 8;
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = 0.f;
+      if (n0 + c8 < p.N) {  // N % 8 == 0: the 16-byte load is all-in or all-out
+        const T* src = (which ? zr : sc) + static_cast<int64_t>(grp_lo + gi) * p.N + n0 + c8;
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(src));
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = unpack2<T>(w[e]);
+          v[2 * e] = which ? f.x - MG::kMagic : f.x;
+          v[2 * e + 1] = which ? f.y - MG::kMagic : f.y;
+        }
       }
-      szf[(gi * 2 + which) * 128 + c] = v;
+      float4* dst = reinterpret_cast<float4*>(szf + (gi * 2 + which) * 128 + c8);
+      dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+      dst[1] = make_float4(v[4], v[5], v[6], v[7]);
     }
   }
   griddep_wait();  // x is written by the previous kernel
-  // ---- 3. x slice: MT * 8 token rows (rows >= M zero) x nkb * 64 k; warp w stages rows w, w + 8.
-  //         f16: elements with k % 4 in {2, 3} are stored times 1/16 (see the header comment).
+  // ---- 3. x slice: the M real token rows x nkb * 64 k, then ONE zero row that stands in for every
+  //         token >= M of the 8-token MMA tiles.  f16: elements with k % 4 in {2, 3} are stored
+  //         times 1/16 (see the header comment).
+  const int rows = min(p.M, MT * 8);
   {
     const T* xg = static_cast<const T*>(p.x);
     const int cpr = nkb * 8;  // 16-byte chunks per row
-#pragma unroll
-    for (int rr = 0; rr < MT; ++rr) {
-      const int r = warp + rr * 8;
-      const bool ok = r < p.M;
-      const uint4* src = reinterpret_cast<const uint4*>(xg + static_cast<int64_t>(ok ? r : 0) * p.ldx +
+    for (int r = warp; r <= rows; r += 8) {
+      const bool real = r < rows;
+      const uint4* src = reinterpret_cast<const uint4*>(xg + static_cast<int64_t>(real ? r : 0) * p.ldx +
                                                         kb0 * 64);
       uint8_t* dst = smem + r * p.xs_stride;
       for (int c = lane; c < cpr; c += 32) {
-        uint4 v = ok ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+        uint4 v = real ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
         if (MG::kNoShift) {
           v.y = g2_hmul2(v.y, MG::kInv16);
           v.w = g2_hmul2(v.w, MG::kInv16);
@@ -208,9 +220,14 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
   }
   __syncthreads();
 
+  // per-thread activation row addresses (token g of tile m, or the zero row) + this lane's 16 bytes
+  uint32_t xrow[MT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+    xrow[m] = sbase + ((m * 8 + g) < rows ? (m * 8 + g) : rows) * p.xs_stride + t * 16;
+
   // ---- 4. per (group, token) activation sums: sums[gl][0][tok] = MAGIC * sum x', [gl][1][tok] = sum x
-  const int steps_per_group = p.group >> 5;
-  const uint32_t xrow = sbase + g * p.xs_stride + t * 16;  // + mt * 8 rows, + 64 bytes per step
+  const int steps_per_group = SPG ? SPG : (p.group >> 5);
   float* sums = reinterpret_cast<float*>(smem + p.sum_off);
   {
     const uint32_t ones = MG::kOnes, sixteen = MG::kSixteen;
@@ -220,7 +237,7 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
       for (int m = 0; m < MT; ++m) {
         float sp[4] = {0.f, 0.f, 0.f, 0.f}, stt[4] = {0.f, 0.f, 0.f, 0.f};
         for (int s = 0; s < steps_per_group; ++s) {
-          const uint4 xb = lds128(xrow + m * 8 * p.xs_stride + (st0 + s) * 64);
+          const uint4 xb = lds128(xrow[m] + (st0 + s) * 64);
           g2_mma<T>(sp, ones, ones, ones, ones, xb.x, xb.y);
           g2_mma<T>(sp, ones, ones, ones, ones, xb.z, xb.w);
           if (MG::kNoShift) {
@@ -247,85 +264,94 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
     for (int e = 0; e < 4; ++e) out[m][e] = acc[m][e] = 0.f;
 
   const uint32_t kMagic = g2_opaque(MG::kBits);
-  const uint32_t kMaskLo = g2_opaque(0x000f000fu);
-  const uint32_t kMaskHi = g2_opaque(0x00f000f0u);
-  int in_group = 0, gl = 0;
-  const float* szp = reinterpret_cast<const float*>(smem + p.sz_off) + warp * 16 + g;
-  const float* sump = sums + 2 * t;
+  const float* szrow = reinterpret_cast<const float*>(smem + p.sz_off) + warp * 16 + g;  // +256 / group
+  const float* sumrow = sums + 2 * t;                                                   // +2*MT*8 / group
+  int in_group = 0;  // SPG == 0 only
 
-  auto step = [&](uint32_t wa, uint32_t wb, int st) {  // one 32-k step: words of column g / g + 8
+  // fold of a finished group: out += s * (acc - MAGIC * sum x' - z * sum x)
+  auto fold = [&]() {
+    const float s_lo = szrow[0], s_hi = szrow[8], z_lo = szrow[128], z_hi = szrow[136];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const float2 mp = *reinterpret_cast<const float2*>(sumrow + m * 8);
+      const float2 sx = *reinterpret_cast<const float2*>(sumrow + MT * 8 + m * 8);
+      out[m][0] = fmaf(s_lo, fmaf(-z_lo, sx.x, acc[m][0] - mp.x), out[m][0]);
+      out[m][1] = fmaf(s_lo, fmaf(-z_lo, sx.y, acc[m][1] - mp.y), out[m][1]);
+      out[m][2] = fmaf(s_hi, fmaf(-z_hi, sx.x, acc[m][2] - mp.x), out[m][2]);
+      out[m][3] = fmaf(s_hi, fmaf(-z_hi, sx.y, acc[m][3] - mp.y), out[m][3]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[m][e] = 0.f;
+    }
+    szrow += 256;
+    sumrow += 2 * MT * 8;
+  };
+  // one 32-k step: wa / wb = the words of columns g / g + 8, xoff = byte offset of the step's x
+  auto step = [&](uint32_t wa, uint32_t wb, uint32_t xoff, bool fold_here) {
     uint4 xb[MT];
 #pragma unroll
-    for (int m = 0; m < MT; ++m) xb[m] = lds128(xrow + m * 8 * p.xs_stride + st * 64);
+    for (int m = 0; m < MT; ++m) xb[m] = lds128(xrow[m] + xoff);
     uint32_t a0, a1, a2, a3, c0, c1, c2, c3;
-    a0 = g2_and_or(wa, kMaskLo, kMagic);
-    a1 = g2_and_or(wb, kMaskLo, kMagic);
+    a0 = g2_and_or(wa, 0x000f000fu, kMagic);
+    a1 = g2_and_or(wb, 0x000f000fu, kMagic);
     if (MG::kNoShift) {
-      a2 = g2_and_or(wa, kMaskHi, kMagic);
-      a3 = g2_and_or(wb, kMaskHi, kMagic);
+      a2 = g2_and_or(wa, 0x00f000f0u, kMagic);
+      a3 = g2_and_or(wb, 0x00f000f0u, kMagic);
       const uint32_t wa8 = wa >> 8, wb8 = wb >> 8;
-      c0 = g2_and_or(wa8, kMaskLo, kMagic);
-      c1 = g2_and_or(wb8, kMaskLo, kMagic);
-      c2 = g2_and_or(wa8, kMaskHi, kMagic);
-      c3 = g2_and_or(wb8, kMaskHi, kMagic);
+      c0 = g2_and_or(wa8, 0x000f000fu, kMagic);
+      c1 = g2_and_or(wb8, 0x000f000fu, kMagic);
+      c2 = g2_and_or(wa8, 0x00f000f0u, kMagic);
+      c3 = g2_and_or(wb8, 0x00f000f0u, kMagic);
     } else {
-      a2 = g2_and_or(wa >> 4, kMaskLo, kMagic);
-      a3 = g2_and_or(wb >> 4, kMaskLo, kMagic);
-      c0 = g2_and_or(wa >> 8, kMaskLo, kMagic);
-      c1 = g2_and_or(wb >> 8, kMaskLo, kMagic);
-      c2 = g2_and_or(wa >> 12, kMaskLo, kMagic);
-      c3 = g2_and_or(wb >> 12, kMaskLo, kMagic);
+      a2 = g2_and_or(wa >> 4, 0x000f000fu, kMagic);
+      a3 = g2_and_or(wb >> 4, 0x000f000fu, kMagic);
+      c0 = g2_and_or(wa >> 8, 0x000f000fu, kMagic);
+      c1 = g2_and_or(wb >> 8, 0x000f000fu, kMagic);
+      c2 = g2_and_or(wa >> 12, 0x000f000fu, kMagic);
+      c3 = g2_and_or(wb >> 12, 0x000f000fu, kMagic);
     }
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
       g2_mma<T>(acc[m], a0, a1, a2, a3, xb[m].x, xb[m].y);
       g2_mma<T>(acc[m], c0, c1, c2, c3, xb[m].z, xb[m].w);
     }
-    if (++in_group == steps_per_group) {
-      // fold the finished group: out += s * (acc - MAGIC * sum x' - z * sum x), z = (MAGIC + z) - MAGIC
-      const float* row = szp + gl * 256;
-      const float s_lo = row[0], s_hi = row[8], z_lo = row[128], z_hi = row[136];
-      const float* sm = sump + gl * 2 * (MT * 8);
-#pragma unroll
-      for (int m = 0; m < MT; ++m) {
-        const float2 mp = *reinterpret_cast<const float2*>(sm + m * 8);
-        const float2 sx = *reinterpret_cast<const float2*>(sm + MT * 8 + m * 8);
-        out[m][0] = fmaf(s_lo, fmaf(-z_lo, sx.x, acc[m][0] - mp.x), out[m][0]);
-        out[m][1] = fmaf(s_lo, fmaf(-z_lo, sx.y, acc[m][1] - mp.y), out[m][1]);
-        out[m][2] = fmaf(s_hi, fmaf(-z_hi, sx.x, acc[m][2] - mp.x), out[m][2]);
-        out[m][3] = fmaf(s_hi, fmaf(-z_hi, sx.y, acc[m][3] - mp.y), out[m][3]);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) acc[m][e] = 0.f;
-      }
+    if (SPG) {
+      if (fold_here) fold();
+    } else if (++in_group == steps_per_group) {
       in_group = 0;
-      ++gl;
+      fold();
     }
   };
+  // tile j of a round (64 k = two steps); with a compile-time SPG a round of 6 tiles = 12 steps starts
+  // on a group boundary (12 % SPG == 0), so the fold positions are compile-time too
+  auto tile = [&](const uint4& w, int j, uint32_t xround) {
+    step(w.x, w.y, xround + j * 128, SPG && ((2 * j + 1) % SPG == 0));
+    step(w.z, w.w, xround + j * 128 + 64, SPG && ((2 * j + 2) % SPG == 0));
+  };
+  static_assert(SPG == 0 || (2 * kG2Depth) % SPG == 0, "a round must hold whole groups");
 
   if (warp_ok) {
     int base = 0;
-    // steady state: every block of this round has a successor kG2Depth blocks ahead
+    const uint4* wq = wp + kG2Depth * 32;  // the tile kG2Depth ahead of the round's first
+    uint32_t xround = 0;
+    // steady state: every tile of this round has a successor kG2Depth tiles ahead
 #pragma unroll 1
-    for (; base + 2 * kG2Depth <= nkb; base += kG2Depth) {
+    for (; base + 2 * kG2Depth <= nkb; base += kG2Depth, wq += kG2Depth * 32, xround += kG2Depth * 128) {
 #pragma unroll
       for (int j = 0; j < kG2Depth; ++j) {
         const uint4 w = buf[j];
-        buf[j] = g2_ldg_stream(wp + (base + j + kG2Depth) * 32);
-        step(w.x, w.y, 2 * (base + j));
-        step(w.z, w.w, 2 * (base + j) + 1);
+        buf[j] = g2_ldg_stream(wq + j * 32);
+        tile(w, j, xround);
       }
     }
     // tail: at most two rounds, loads predicated
 #pragma unroll 1
-    for (; base < nkb; base += kG2Depth) {
+    for (; base < nkb; base += kG2Depth, wq += kG2Depth * 32, xround += kG2Depth * 128) {
 #pragma unroll
       for (int j = 0; j < kG2Depth; ++j) {
-        const int kb = base + j;
-        if (kb < nkb) {
+        if (base + j < nkb) {
           const uint4 w = buf[j];
-          if (kb + kG2Depth < nkb) buf[j] = g2_ldg_stream(wp + (kb + kG2Depth) * 32);
-          step(w.x, w.y, 2 * kb);
-          step(w.z, w.w, 2 * kb + 1);
+          if (base + j + kG2Depth < nkb) buf[j] = g2_ldg_stream(wq + j * 32);
+          tile(w, j, xround);
         }
       }
     }
@@ -440,7 +466,7 @@ static bool gemv2_plan(int M, int N, int K, int group, Gemv2Plan* pl) {
     pl->S = S;
     pl->kb_per_rank = kb_per_rank;
     pl->xs_stride = xs_stride;
-    pl->sz_off = MT * 8 * xs_stride;
+    pl->sz_off = (M + 1) * xs_stride;  // M token rows + the shared zero row
     pl->sum_off = pl->sz_off + ng * 1024;
     pl->part_off = pl->sum_off + ng * 2 * MT * 8 * 4;
     pl->smem = pl->part_off + MT * 8 * 128 * 4;
@@ -516,20 +542,25 @@ int b200_w4a16_gemv_v2(const void* x, int64_t ldx, const void* qweight_stream, c
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int n_groups = ceil_div(N, 128);
   void (*kern)(const Gemv2Params) = nullptr;
-  int ai = 0;
-  if (dtype == B200_F16) {
-    kern = M <= 8 ? w4a16_gemv2_kernel<__half, 1> : w4a16_gemv2_kernel<__half, 2>;
-    ai = M <= 8 ? 0 : 1;
-  } else {
-    kern = M <= 8 ? w4a16_gemv2_kernel<__nv_bfloat16, 1> : w4a16_gemv2_kernel<__nv_bfloat16, 2>;
-    ai = M <= 8 ? 2 : 3;
-  }
-  static int attr_smem[4] = {0, 0, 0, 0};
+  const int spg = group_size == 128 ? 4 : group_size == 64 ? 2 : group_size == 32 ? 1 : 0;
+  const int mt = M <= 8 ? 1 : 2;
+#define B200_G2_PICK(T_, MT_)                                                             \
+  (spg == 4   ? w4a16_gemv2_kernel<T_, MT_, 4>                                            \
+   : spg == 2 ? w4a16_gemv2_kernel<T_, MT_, 2>                                            \
+   : spg == 1 ? w4a16_gemv2_kernel<T_, MT_, 1>                                            \
+              : w4a16_gemv2_kernel<T_, MT_, 0>)
+  if (dtype == B200_F16)
+    kern = mt == 1 ? B200_G2_PICK(__half, 1) : B200_G2_PICK(__half, 2);
+  else
+    kern = mt == 1 ? B200_G2_PICK(__nv_bfloat16, 1) : B200_G2_PICK(__nv_bfloat16, 2);
+#undef B200_G2_PICK
+  const int ai = (dtype == B200_F16 ? 0 : 8) + (mt - 1) * 4 + (spg == 4 ? 3 : spg);
+  static int attr_smem[16] = {};
   if (pl.smem > attr_smem[ai]) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.smem));
     attr_smem[ai] = pl.smem;
   }
-  note_variant("w4a16_gemv2 mt=%d splits=%d tiles=%d", M <= 8 ? 1 : 2, pl.S, n_groups);
+  note_variant("w4a16_gemv2 mt=%d spg=%d splits=%d tiles=%d", mt, spg, pl.S, n_groups);
   {
     ScopedKernelTimer timer("w4a16_gemv2", st);
     B200_CUDA_OK(launch_kernel(kern, dim3(n_groups * pl.S), dim3(kG2Threads), pl.smem, st, pl.S,

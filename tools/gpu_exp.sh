@@ -3,7 +3,7 @@
 # gpurun_out/, what is worth keeping is copied to profiles/ by hand).  Run: gpurun -- bash tools/gpu_exp.sh
 set -u
 out=gpurun_out
-tag=${GPU_TAG:-r02a}
+tag=${GPU_TAG:-r02b}
 mkdir -p $out
 t0=$(date +%s)
 stamp() { echo "== $1 (+$(( $(date +%s) - t0 )) s)"; }
@@ -16,7 +16,7 @@ stamp "bench fused tail (default)"
 timeout 600 python bench.py --no-cpu-baseline > $out/${tag}_bench_fused.json 2> $out/${tag}_bench_fused.err; echo "rc=$?"
 python - <<'EOF'
 import json,sys
-for f in ["gpurun_out/%s_bench_fused.json" % __import__("os").environ.get("GPU_TAG","r02a")]:
+for f in ["gpurun_out/%s_bench_fused.json" % __import__("os").environ.get("GPU_TAG","r02b")]:
     try:
         d=json.loads(open(f).read().strip().splitlines()[-1])
         print(f, d["ms_per_step"], d["value"], json.dumps(d.get("kernel_split_eager")), d["roofline"]["us_per_launch"])
