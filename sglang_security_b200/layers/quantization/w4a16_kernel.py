@@ -120,9 +120,9 @@ def w4a16_gemv_v2_config(splits: int = 0) -> None:
     _lib.check(_lib.load().b200_w4a16_gemv_v2_config(int(splits)), "b200_w4a16_gemv_v2_config")
 
 
-# largest token count handed to the stream GEMV (the kernel accepts up to 16; the two-tile instance
-# for 9..16 tokens is not yet ahead of the tcgen05 swap-AB kernel, profiles/r02_bench_w4a16_gemv2_*.json)
-GEMV_V2_MAX_M = int(os.environ.get("B200_W4A16_GEMV2_MAX_M", "8"))
+# largest token count handed to the stream GEMV (its two-tile instance for 9..16 tokens is at par or
+# ahead of the tcgen05 swap-AB kernel on every cfg-4 shape, profiles/r02_bench_w4a16_gemv2.json)
+GEMV_V2_MAX_M = int(os.environ.get("B200_W4A16_GEMV2_MAX_M", "16"))
 
 
 def stream_copy_enabled() -> bool:
