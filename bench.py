@@ -354,7 +354,8 @@ def run_b200(args):
         step()
     torch.cuda.synchronize()
     _lib.timing_enable(False)
-    kernel_names = ("attn_decode_split", "attn_decode_fp8kv", "attn_merge", "rope_kv_write", "kv_write",
+    kernel_names = ("attn_decode_split", "attn_decode_fp8kv", "attn_merge", "attn_merge_quant", "dense_gemm",
+                    "rope_kv_write", "kv_write",
                     "kv_write_fp8", "rmsnorm", "silu_and_mul", "fp8_quant", "fp8_gemm_smallm",
                     "fp8_gemm", "all_reduce_ll", "all_reduce_oneshot", "all_reduce_nvls")
     split = {}

@@ -135,7 +135,10 @@ int b200_attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
  * q_scales [bs] fp32): the o_proj input quantiser of Fp8LinearMethod.apply (fp8_utils.py:454-648)
  * disappears from the decode step.  `tickets`: b200_attn_decode_fused_ticket_bytes(bs, Hq, Hkv) bytes
  * of device memory, zero before the first call; the counters re-arm themselves, so CUDA-graph
- * replays need no memset.  Requires num_splits > 1 or q_out != NULL.                             */
+ * replays need no memset.  Requires num_splits > 1 or q_out != NULL.
+ * tickets == NULL selects the two-launch form of the same result: the split kernel followed by ONE
+ * merge(+quantise) kernel (one CTA per request) instead of b200_attn_merge + the quantiser —
+ * the better choice once the split kernel is bandwidth-bound (large batch x context).           */
 int b200_attn_decode_fused(const void* q, int64_t q_stride, const void* k_cache,
                            const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
                            const int32_t* req_to_token, int64_t req_to_token_stride,

@@ -582,6 +582,104 @@ __global__ void attn_merge_kernel(const float* __restrict__ part_o,
   }
 }
 
+// Merge of split partials for ALL heads of a request + per-token FP8 quantisation of the merged
+// row in one launch: one CTA per request.  Replaces attn_merge_kernel followed by
+// fp8_quant_per_token_kernel (same arithmetic in the same order, so the bytes are identical); with
+// num_splits == 1 it only quantises the row the split kernel wrote.  The row (T) lives in dynamic
+// shared memory between the amax pass and the quantising pass.
+template <typename T>
+__global__ void __launch_bounds__(256)
+attn_merge_quant_kernel(const float* __restrict__ part_o, const float* __restrict__ part_lse,
+                        T* __restrict__ o, int64_t o_stride, int write_o, uint8_t* __restrict__ q_out,
+                        int64_t q_stride, float* __restrict__ q_scales,
+                        const int64_t* __restrict__ seq_lens, int Hq, int Dv, int num_splits,
+                        int align) {
+  extern __shared__ __align__(16) uint8_t mq_smem[];
+  __shared__ float red[8];
+  griddep_wait();
+  griddep_launch_dependents();
+  const int b = blockIdx.x;
+  const int len = static_cast<int>(seq_lens[b]);
+  if (len <= 0) return;
+  T* row = reinterpret_cast<T*>(mq_smem);
+  T* orow = o + static_cast<int64_t>(b) * o_stride;
+  const int n4 = Hq * Dv / 4;
+  const int chunk = split_chunk(len, num_splits, align);
+  const int nvalid = ceil_div(len, chunk);
+  float amax = 0.f;
+  for (int it = threadIdx.x; it < n4; it += 256) {
+    const int e0 = it * 4, h = e0 / Dv, d = e0 - h * Dv;
+    uint2 pk;
+    if (num_splits > 1) {
+      const int64_t base = (static_cast<int64_t>(b) * Hq + h) * num_splits;
+      float M = -INFINITY;
+      for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldg(part_lse + base + s));
+      float den = 0.f, num[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int s = 0; s < nvalid; ++s) {
+        const float w = fast_exp2(__ldg(part_lse + base + s) - M);
+        const float4 x = __ldg(reinterpret_cast<const float4*>(part_o + (base + s) * Dv + d));
+        den += w;
+        num[0] += w * x.x;
+        num[1] += w * x.y;
+        num[2] += w * x.z;
+        num[3] += w * x.w;
+      }
+      const float inv = 1.f / den;
+      pk.x = pack2<T>(num[0] * inv, num[1] * inv);
+      pk.y = pack2<T>(num[2] * inv, num[3] * inv);
+      if (write_o) *reinterpret_cast<uint2*>(orow + e0) = pk;
+    } else {
+      pk = *reinterpret_cast<const uint2*>(orow + e0);
+    }
+    *reinterpret_cast<uint2*>(row + e0) = pk;
+    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
+    amax = fmaxf(fmaxf(amax, fmaxf(fabsf(a.x), fabsf(a.y))), fmaxf(fabsf(c.x), fabsf(c.y)));
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = amax;
+  __syncthreads();
+  amax = red[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) amax = fmaxf(amax, red[w]);
+  const float scale = amax / 448.0f;
+  if (threadIdx.x == 0) q_scales[b] = scale;
+  const float inv = scale > 0.f ? 1.0f / scale : 0.f;
+  uint8_t* qrow = q_out + static_cast<int64_t>(b) * q_stride;
+  for (int it = threadIdx.x; it < n4; it += 256) {  // each thread re-reads what it wrote itself
+    const uint2 pk = *reinterpret_cast<const uint2*>(row + it * 4);
+    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
+    const float x0 = fmaxf(fminf(a.x * inv, 448.0f), -448.0f), x1 = fmaxf(fminf(a.y * inv, 448.0f), -448.0f);
+    const float x2 = fmaxf(fminf(c.x * inv, 448.0f), -448.0f), x3 = fmaxf(fminf(c.y * inv, 448.0f), -448.0f);
+    uint16_t lo, hi;
+    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(lo) : "f"(x1), "f"(x0));
+    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(hi) : "f"(x3), "f"(x2));
+    *reinterpret_cast<uint32_t*>(qrow + it * 4) = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+  }
+}
+
+template <typename T>
+static int launch_merge_quant(const DecodeParams& p, int Dv, int align, cudaStream_t st) {
+  const size_t smem = static_cast<size_t>(p.Hq) * Dv * sizeof(T);
+  B200_REQUIRE(smem <= 160 * 1024, "attn_merge_quant: row of %d x %d does not fit shared memory", p.Hq, Dv);
+  auto kern = attn_merge_quant_kernel<T>;
+  static size_t attr = 0;
+  if (smem > attr && smem > 48 * 1024) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(smem)));
+    attr = smem;
+  }
+  {
+    ScopedKernelTimer timer("attn_merge_quant", st);
+    B200_CUDA_OK(launch_kernel(kern, dim3(p.bs), dim3(256), smem, st, 1, pdl_family(p.bs, kPdlMerge),
+                               static_cast<const float*>(p.part_o), static_cast<const float*>(p.part_lse),
+                               static_cast<T*>(p.o), p.o_stride, 1, p.q_out, p.q_out_stride, p.q_scales,
+                               p.seq_lens, p.Hq, Dv, p.num_splits, align));
+  }
+  B200_CHECK_LAUNCH("attn_merge_quant_kernel");
+  return 0;
+}
+
 // ---- host-side dispatch -----------------------------------------------------------------------
 // One instance family, tuned on the B200 for the HBM-bound regime (profiles/r01_decode_tuning.md):
 // 16-token tiles, 2 stages, 3 warps -> 48 KiB per CTA at D=128, 4 CTAs (12 warps) per SM.  More
@@ -723,7 +821,7 @@ static int apply_tail(DecodeParams& p, const DecodeTail* tail, int D, const char
   p.q_scales = nullptr;
   if (!tail) return 0;
   const size_t need = static_cast<size_t>(p.bs) * (1 + p.Hkv * p.head_tiles) * sizeof(unsigned);
-  B200_REQUIRE(tail->tickets && tail->ticket_bytes >= need,
+  B200_REQUIRE(!tail->tickets || tail->ticket_bytes >= need,
                "%s: ticket buffer too small (%zu < %zu bytes)", who, tail->ticket_bytes, need);
   B200_REQUIRE((tail->q_out == nullptr) == (tail->q_scales == nullptr),
                "%s: q_out and q_scales go together", who);
@@ -733,7 +831,7 @@ static int apply_tail(DecodeParams& p, const DecodeTail* tail, int D, const char
                "%s: q_out must be 8-byte aligned with q_out_stride %% 8 == 0", who);
   B200_REQUIRE(p.o_stride % 8 == 0 && aligned16(p.o) && (p.Hq * D) % 8 == 0,
                "%s: o must be 16-byte aligned with o_stride %% 8 == 0", who);
-  p.tickets = static_cast<unsigned*>(tail->tickets);
+  p.tickets = static_cast<unsigned*>(tail->tickets);  // null: the tail is one merge(+quant) launch
   p.q_out = static_cast<uint8_t*>(tail->q_out);
   p.q_out_stride = tail->q_out_stride;
   p.q_scales = tail->q_scales;
@@ -837,7 +935,10 @@ static int attn_decode_impl(const void* q, int64_t q_stride, const void* k_cache
   int rc = dtype == B200_BF16 ? dispatch_decode<__nv_bfloat16>(p, D, G, st)
                               : dispatch_decode<__half>(p, D, G, st);
   if (rc) return rc;
-  if (num_splits > 1 && !tail)
+  if (tail && !tail->tickets && tail->q_out)
+    return dtype == B200_BF16 ? launch_merge_quant<__nv_bfloat16>(p, Dv, decode_align(), st)
+                              : launch_merge_quant<__half>(p, Dv, decode_align(), st);
+  if (num_splits > 1 && !(tail && tail->tickets))
     return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
                            decode_align(), dtype, stream);
   return 0;
@@ -935,7 +1036,10 @@ static int attn_decode_fp8kv_impl(const void* q, int64_t q_stride, const void* k
   const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, st)
                                     : dispatch_decode_fp8kv<__half>(p, D, G, st);
   if (rc) return rc;
-  if (num_splits > 1 && !tail)
+  if (tail && !tail->tickets && tail->q_out)
+    return dtype == B200_BF16 ? launch_merge_quant<__nv_bfloat16>(p, Dv, decode_align_fp8kv(), st)
+                              : launch_merge_quant<__half>(p, Dv, decode_align_fp8kv(), st);
+  if (num_splits > 1 && !(tail && tail->tickets))
     return b200_attn_merge(p.part_o, p.part_lse, o, o_stride, seq_lens, bs, Hq, Dv, num_splits,
                            decode_align_fp8kv(), dtype, stream);
   return 0;

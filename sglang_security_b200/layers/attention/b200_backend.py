@@ -75,7 +75,13 @@ class B200AttnBackend(AttentionBackend):
         self._graph_workspace: Optional[torch.Tensor] = None
         self._graph_max_bs = 0
         # fused decode tail (merge + optional o_proj input quantisation by the last CTA of a request)
+        # fused_tail: False = split + merge kernels and a separate quantiser (the reference's launch
+        # structure).  True = the tail is fused: inside the split kernel (ticket counters) while the
+        # step is latency-bound, i.e. batch <= tail_in_kernel_max_bs, else as ONE merge+quantise launch
+        # (in-kernel tails cost the bandwidth-bound split kernel more than the launch they save:
+        # 8.93 vs 8.72 ms per step at batch 64 x 4k, profiles/r02_notes.md)
         self.fused_tail = os.environ.get("B200_ATTN_FUSED_TAIL", "1") != "0"
+        self.tail_in_kernel_max_bs = int(os.environ.get("B200_ATTN_TAIL_IN_KERNEL_MAX_BS", "16"))
         self._tickets = torch.zeros(256 * (1 + self.num_head), dtype=torch.int32, device=self.device)
 
     def _ticket_buffer(self, bs: int) -> torch.Tensor:
@@ -275,9 +281,10 @@ class B200AttnBackend(AttentionBackend):
                 qa = torch.empty((bs, hq * dv), dtype=torch.float8_e4m3fn, device=q.device)
                 sa = torch.empty((bs, 1), dtype=torch.float32, device=q.device)
             fn = self.lib.b200_attn_decode_fp8kv_fused if fp8kv else self.lib.b200_attn_decode_fused
-            tickets = self._ticket_buffer(bs)
-            rc = fn(*common, tickets.data_ptr(), tickets.numel() * 4, _lib.ptr(qa),
-                    0 if qa is None else qa.stride(0), _lib.ptr(sa), _lib.current_stream())
+            tickets = self._ticket_buffer(bs) if bs <= self.tail_in_kernel_max_bs else None
+            rc = fn(*common, _lib.ptr(tickets), 0 if tickets is None else tickets.numel() * 4,
+                    _lib.ptr(qa), 0 if qa is None else qa.stride(0), _lib.ptr(sa),
+                    _lib.current_stream())
             _lib.check(rc, "b200_attn_decode_fused")
             if fp8_out:
                 from ..quantization.fp8_utils import QuantizedActivation

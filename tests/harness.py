@@ -49,7 +49,7 @@ def make_model_runner(case, device="cuda", layer_num=1, num_kv_splits=0):
 
 
 def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype=None,
-             fused_tail=None, fp8_out=False, repeat=1):
+             fused_tail=None, fp8_out=False, repeat=1, tail_in_kernel=None):
     """CUDA path: B200AttnBackend through RadixAttention.forward, KV write included."""
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
     from sglang_security_b200.layers.radix_attention import RadixAttention
@@ -60,6 +60,8 @@ def b200_run(case, logit_cap=0.0, num_kv_splits=0, strided_qkv=True, index_dtype
     backend = B200AttnBackend(mr)
     if fused_tail is not None:
         backend.fused_tail = fused_tail
+    if tail_in_kernel is not None:   # force the in-kernel (ticket) tail or the one-launch tail
+        backend.tail_in_kernel_max_bs = 1 << 30 if tail_in_kernel else 0
     layer = RadixAttention(case.hq, case.d, float(case.d) ** -0.5, case.hkv, 0, logit_cap=logit_cap)
     t = case.q.shape[0]
     if strided_qkv:

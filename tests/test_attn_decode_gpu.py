@@ -218,7 +218,8 @@ def test_decode_full_size_properties():
 # ---- fused tail: merge (+ o_proj input quantisation) by the last CTA of each request ---------------
 @pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (8, 1, 128), (64, 8, 128)])
 @pytest.mark.parametrize("splits", [1, 2, 5])
-def test_decode_fused_tail_equals_split_plus_merge_plus_quant(hq, hkv, d, splits):
+@pytest.mark.parametrize("in_kernel", [True, False])
+def test_decode_fused_tail_equals_split_plus_merge_plus_quant(hq, hkv, d, splits, in_kernel):
     """The fused tail must reproduce the three-launch chain bit for bit: merged 16-bit row ==
     b200_attn_merge's, e4m3 bytes and fp32 scales == b200_fp8_quant_per_token of that row; three
     back-to-back calls prove the ticket counters re-arm themselves (ragged lengths incl. requests
@@ -228,9 +229,11 @@ def test_decode_fused_tail_equals_split_plus_merge_plus_quant(hq, hkv, d, splits
     case = scenarios.make_attention_case(seed=11 * hq + d + splits, hq=hq, hkv=hkv, d=d,
                                          seq_lens=[1, 47, 48, 49, 300, 1025, 700, 96], shared_prefix=16)
     o_plain, _, _ = harness.b200_run(case, num_kv_splits=splits, fused_tail=False)
-    o_fused, _, _ = harness.b200_run(case, num_kv_splits=splits, fused_tail=True, repeat=3)
+    o_fused, _, _ = harness.b200_run(case, num_kv_splits=splits, fused_tail=True, repeat=3,
+                                     tail_in_kernel=in_kernel)
     assert torch.equal(o_plain.view(torch.int16), o_fused.view(torch.int16))
-    (qa, sa), _, _ = harness.b200_run(case, num_kv_splits=splits, fused_tail=True, fp8_out=True, repeat=3)
+    (qa, sa), _, _ = harness.b200_run(case, num_kv_splits=splits, fused_tail=True, fp8_out=True, repeat=3,
+                                      tail_in_kernel=in_kernel)
     q_ref, s_ref = sglang_per_token_quant_fp8(o_plain.cuda())
     assert torch.equal(sa, s_ref.cpu())
     assert torch.equal(qa.view(torch.uint8), q_ref.cpu().view(torch.uint8))
@@ -244,7 +247,7 @@ def test_decode_fused_tail_full_batch_against_oracle():
     case = scenarios.make_attention_case(seed=77, hq=32, hkv=8, d=128,
                                          seq_lens=[257 + 13 * i for i in range(64)], shared_prefix=128)
     o_ref, _, _ = harness.oracle_run(case)
-    o, _, _ = harness.b200_run(case, num_kv_splits=4, fused_tail=True, repeat=2)
+    o, _, _ = harness.b200_run(case, num_kv_splits=4, fused_tail=True, repeat=2, tail_in_kernel=True)
     st = harness.error_stats(o, o_ref)
     assert st["max_abs"] <= MAX_ABS and st["rel_l2"] <= REL_L2, st
 

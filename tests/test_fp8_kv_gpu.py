@@ -53,7 +53,8 @@ def test_kv_write_fp8_bit_exact(dtype, scales):
     assert torch.equal(qkv.cpu()[:, :hkv * d], k.reshape(t, -1))  # source left untouched
 
 
-def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0, fused_tail=None, fp8_out=False):
+def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0, fused_tail=None, fp8_out=False,
+                tail_in_kernel=None):
     """-> (o_gpu, o_oracle, k bytes gpu, k bytes oracle)"""
     import harness
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
@@ -87,6 +88,8 @@ def _run_decode(case, k_scale, v_scale, num_kv_splits, logit_cap=0.0, fused_tail
     backend = B200AttnBackend(mr)
     if fused_tail is not None:
         backend.fused_tail = fused_tail
+    if tail_in_kernel is not None:
+        backend.tail_in_kernel_max_bs = 1 << 30 if tail_in_kernel else 0
     t = case.q.shape[0]
     qkv = torch.cat([case.q, case.k_new.reshape(t, -1), case.v_new.reshape(t, -1)], dim=1).cuda()
     q, k, v = qkv.split([case.hq * case.d, case.hkv * case.d, case.hkv * case.d], dim=-1)
@@ -191,16 +194,18 @@ def test_extend_fp8kv_matches_oracle(hq, hkv, d, scales):
 
 
 @pytest.mark.parametrize("splits", [1, 3])
-def test_decode_fp8kv_fused_tail_equals_unfused(splits):
+@pytest.mark.parametrize("in_kernel", [True, False])
+def test_decode_fp8kv_fused_tail_equals_unfused(splits, in_kernel):
     """FP8-KV decode: fused merge + per-token quantisation tail == split + merge (+ quantiser)."""
     from sglang_security_b200.layers.quantization.fp8_kernel import sglang_per_token_quant_fp8
 
     case = scenarios.make_attention_case(seed=41 + splits, hq=32, hkv=8, d=128,
                                          seq_lens=[1, 95, 96, 97, 700, 1025], shared_prefix=20)
     o_plain, _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=False)
-    o_fused, _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True)
+    o_fused, _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True, tail_in_kernel=in_kernel)
     assert torch.equal(o_plain.view(torch.int16), o_fused.view(torch.int16))
-    (qa, sa), _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True, fp8_out=True)
+    (qa, sa), _, _, _ = _run_decode(case, 0.25, 1.5, splits, fused_tail=True, fp8_out=True,
+                                    tail_in_kernel=in_kernel)
     q_ref, s_ref = sglang_per_token_quant_fp8(o_plain.cuda())
     assert torch.equal(sa, s_ref.cpu())
     assert torch.equal(qa.view(torch.uint8), q_ref.cpu().view(torch.uint8))

@@ -4,7 +4,7 @@
 
 One step = embedding lookup -> L x B200DecoderLayer (fused RMSNorm->quant, FP8/INT4/bf16 linear,
 RoPE->KV write, paged decode attention, SiLU*mul->quant; all-reduce after o_proj/down_proj when
-TP > 1) -> final RMSNorm -> lm_head (16-bit library GEMM, outside the hot path) -> greedy argmax,
+TP > 1) -> final RMSNorm -> lm_head (in-tree 16-bit tcgen05 GEMM) -> greedy argmax,
 replayed from one CUDA graph.  Run under torchrun for TP > 1 (one rank per GPU, NCCL).
 
 Prints one JSON line per (batch, context) point: tokens/s, ms/step, the per-kernel time split of an
@@ -100,6 +100,7 @@ def main():
     from sglang_security_b200 import _lib
     from sglang_security_b200.distributed.parallel_state import initialize_model_parallel
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
+    from sglang_security_b200.layers.dense_kernel import gemm_16bit
     from sglang_security_b200.layers.layernorm import RMSNorm
     from sglang_security_b200.layers.rotary_embedding import RotaryEmbedding
     from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
@@ -184,7 +185,7 @@ def main():
             for L in mods:
                 h, residual = L(positions, h, fb, residual)
             h, _ = final_norm(h, residual)
-            logits = F.linear(h, lm_head)
+            logits = gemm_16bit(h, lm_head)
             out_tok.copy_(logits.argmax(-1))
 
         backend.init_forward_metadata(fb)
@@ -201,7 +202,8 @@ def main():
         split = {}
         for name in ("rmsnorm", "fp8_gemm_smallm", "fp8_block_gemm_smallm", "fp8_gemm",
                      "fp8_block_gemm", "w4a16_gemm", "w4a16_gemv", "rope_kv_write",
-                     "attn_decode_split", "attn_decode_fp8kv", "kv_write_fp8", "attn_merge", "all_reduce_ll",
+                     "attn_decode_split", "attn_decode_fp8kv", "kv_write_fp8", "attn_merge",
+                     "attn_merge_quant", "w4a16_gemv2", "dense_gemm", "all_reduce_ll",
                      "all_reduce_oneshot", "fp8_quant", "silu_and_mul", "kv_write"):
             n, ms = _lib.timing_read(name)
             if n:
