@@ -402,6 +402,28 @@ int b200_fp8_gemm_rowcol_ar(void* comm, const void* a, int64_t lda, const void* 
                             int out_dtype, void* stream);
 /* Largest M the *_ar entry points fuse (default 32, measured crossover; max 128; < 0 = default). */
 int b200_comm_fuse_config(int max_m);
+
+/* NVLS: all-reduce with the additions done inside the NVSwitch (multimem.ld_reduce over a multicast
+ * mapping; csrc/comm_nvls.cu).  SURVEY section 8f row 3; reference analogue = the one-shot kernel of
+ * custom_all_reduce.cuh:203-225 (adds on the SM) and NCCL's NVLS algorithms.  Life cycle (host side:
+ * distributed/device_communicators/b200_all_reduce.py):
+ *   b200_nvls_supported()                      1 when device + driver offer multicast objects
+ *   b200_nvls_buffer_bytes(world, bytes)       size rounded to the multicast / allocation granularity
+ *   b200_nvls_create(world, size, &buf, &fd)   rank 0: multicast object + POSIX fd for the peers
+ *   b200_nvls_import(fd, world, size, &buf)    peers: import it (fd passed by SCM_RIGHTS)
+ *   b200_nvls_add_device(buf)                  every rank; host barrier; then
+ *   b200_nvls_bind(buf, &uc, &mc)              every rank: own physical memory bound + both views mapped
+ *   b200_comm_attach_nvls(comm, buf)           b200_comm_all_reduce now uses the switch for messages of
+ *                                              B200_COMM_NVLS_MIN (16 KiB) .. size / 2 bytes
+ *   b200_nvls_free(buf)                                                                           */
+int b200_nvls_supported(void);
+size_t b200_nvls_buffer_bytes(int world, size_t bytes);
+int b200_nvls_create(int world, size_t size, void** buf_out, int* fd_out);
+int b200_nvls_import(int fd, int world, size_t size, void** buf_out);
+int b200_nvls_add_device(void* buf);
+int b200_nvls_bind(void* buf, void** uc_ptr, void** mc_ptr);
+int b200_nvls_free(void* buf);
+int b200_comm_attach_nvls(void* comm, void* nvls_buf);
 int b200_fp8_gemm_block128_ar(void* comm, const void* a, int64_t lda, const void* b, int64_t ldb,
                               const float* as, int64_t as_row_stride, int64_t as_col_stride,
                               const float* bs, int64_t bs_row_stride, const void* bias, void* out,

@@ -97,6 +97,14 @@ _SIGNATURES = {
     "b200_comm_max_bytes": (c_size_t, [c_void_p]),
     "b200_comm_all_reduce": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200_comm_fuse_config": (c_int, [c_int]),
+    "b200_nvls_supported": (c_int, []),
+    "b200_nvls_buffer_bytes": (c_size_t, [c_int, c_size_t]),
+    "b200_nvls_create": (c_int, [c_int, c_size_t, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)]),
+    "b200_nvls_import": (c_int, [c_int, c_int, c_size_t, ctypes.POINTER(c_void_p)]),
+    "b200_nvls_add_device": (c_int, [c_void_p]),
+    "b200_nvls_bind": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p)]),
+    "b200_nvls_free": (c_int, [c_void_p]),
+    "b200_comm_attach_nvls": (c_int, [c_void_p, c_void_p]),
     "b200_fp8_gemm_rowcol_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                         c_int, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
                                         c_int, c_int, c_int, c_void_p]),

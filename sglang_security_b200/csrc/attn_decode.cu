@@ -583,57 +583,70 @@ __global__ void attn_merge_kernel(const float* __restrict__ part_o,
 }
 
 // Merge of split partials for ALL heads of a request + per-token FP8 quantisation of the merged
-// row in one launch: one CTA per request.  Replaces attn_merge_kernel followed by
-// fp8_quant_per_token_kernel (same arithmetic in the same order, so the bytes are identical); with
-// num_splits == 1 it only quantises the row the split kernel wrote.  The row (T) lives in dynamic
-// shared memory between the amax pass and the quantising pass.
+// row in one launch.  Replaces attn_merge_kernel followed by fp8_quant_per_token_kernel (same
+// arithmetic in the same order, so the bytes are identical); with num_splits == 1 it only quantises
+// the row the split kernel wrote.  A request is spread over a CLUSTER of S CTAs (128 threads, one
+// 4-element item per thread and pass), the per-token amax is combined through distributed shared
+// memory (a maximum, so the result does not depend on the split), every value stays in registers
+// between the amax and the quantising pass.
+constexpr int kMqThreads = 128;
+constexpr int kMqMaxItems = 4;  // 4-element items per thread: covers Hq * Dv <= 8 * 128 * 4 * 4
+
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kMqThreads)
 attn_merge_quant_kernel(const float* __restrict__ part_o, const float* __restrict__ part_lse,
-                        T* __restrict__ o, int64_t o_stride, int write_o, uint8_t* __restrict__ q_out,
+                        T* __restrict__ o, int64_t o_stride, uint8_t* __restrict__ q_out,
                         int64_t q_stride, float* __restrict__ q_scales,
                         const int64_t* __restrict__ seq_lens, int Hq, int Dv, int num_splits,
-                        int align) {
-  extern __shared__ __align__(16) uint8_t mq_smem[];
-  __shared__ float red[8];
+                        int align, int per_cta) {
+  __shared__ float red[kMqThreads / 32];
+  __shared__ float cl_slots[8];
+  uint32_t S, rank;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;\n" : "=r"(S));
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(rank));
+  if (S > 1)  // every CTA of the cluster runs before any remote store is issued
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
   griddep_wait();
   griddep_launch_dependents();
-  const int b = blockIdx.x;
+  const int b = blockIdx.x / S;
   const int len = static_cast<int>(seq_lens[b]);
-  if (len <= 0) return;
-  T* row = reinterpret_cast<T*>(mq_smem);
   T* orow = o + static_cast<int64_t>(b) * o_stride;
   const int n4 = Hq * Dv / 4;
-  const int chunk = split_chunk(len, num_splits, align);
-  const int nvalid = ceil_div(len, chunk);
+  const int i0 = static_cast<int>(rank) * per_cta, i1 = min(n4, i0 + per_cta);
+  const int chunk = split_chunk(max(len, 1), num_splits, align);
+  const int nvalid = len > 0 ? ceil_div(len, chunk) : 0;
+  uint2 vals[kMqMaxItems];
   float amax = 0.f;
-  for (int it = threadIdx.x; it < n4; it += 256) {
-    const int e0 = it * 4, h = e0 / Dv, d = e0 - h * Dv;
-    uint2 pk;
-    if (num_splits > 1) {
-      const int64_t base = (static_cast<int64_t>(b) * Hq + h) * num_splits;
-      float M = -INFINITY;
-      for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldg(part_lse + base + s));
-      float den = 0.f, num[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int s = 0; s < nvalid; ++s) {
-        const float w = fast_exp2(__ldg(part_lse + base + s) - M);
-        const float4 x = __ldg(reinterpret_cast<const float4*>(part_o + (base + s) * Dv + d));
-        den += w;
-        num[0] += w * x.x;
-        num[1] += w * x.y;
-        num[2] += w * x.z;
-        num[3] += w * x.w;
+#pragma unroll
+  for (int k = 0; k < kMqMaxItems; ++k) {
+    const int it = i0 + threadIdx.x + k * kMqThreads;
+    vals[k] = make_uint2(0u, 0u);
+    if (it < i1 && len > 0) {
+      const int e0 = it * 4, h = e0 / Dv, d = e0 - h * Dv;
+      if (num_splits > 1) {
+        const int64_t base = (static_cast<int64_t>(b) * Hq + h) * num_splits;
+        float M = -INFINITY;
+        for (int s = 0; s < nvalid; ++s) M = fmaxf(M, __ldg(part_lse + base + s));
+        float den = 0.f, num[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int s = 0; s < nvalid; ++s) {
+          const float w = fast_exp2(__ldg(part_lse + base + s) - M);
+          const float4 x = __ldg(reinterpret_cast<const float4*>(part_o + (base + s) * Dv + d));
+          den += w;
+          num[0] += w * x.x;
+          num[1] += w * x.y;
+          num[2] += w * x.z;
+          num[3] += w * x.w;
+        }
+        const float inv = 1.f / den;
+        vals[k].x = pack2<T>(num[0] * inv, num[1] * inv);
+        vals[k].y = pack2<T>(num[2] * inv, num[3] * inv);
+        *reinterpret_cast<uint2*>(orow + e0) = vals[k];
+      } else {
+        vals[k] = *reinterpret_cast<const uint2*>(orow + e0);
       }
-      const float inv = 1.f / den;
-      pk.x = pack2<T>(num[0] * inv, num[1] * inv);
-      pk.y = pack2<T>(num[2] * inv, num[3] * inv);
-      if (write_o) *reinterpret_cast<uint2*>(orow + e0) = pk;
-    } else {
-      pk = *reinterpret_cast<const uint2*>(orow + e0);
+      const float2 a = unpack2<T>(vals[k].x), c = unpack2<T>(vals[k].y);
+      amax = fmaxf(fmaxf(amax, fmaxf(fabsf(a.x), fabsf(a.y))), fmaxf(fabsf(c.x), fabsf(c.y)));
     }
-    *reinterpret_cast<uint2*>(row + e0) = pk;
-    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
-    amax = fmaxf(fmaxf(amax, fmaxf(fabsf(a.x), fabsf(a.y))), fmaxf(fabsf(c.x), fabsf(c.y)));
   }
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
@@ -641,40 +654,53 @@ attn_merge_quant_kernel(const float* __restrict__ part_o, const float* __restric
   __syncthreads();
   amax = red[0];
 #pragma unroll
-  for (int w = 1; w < 8; ++w) amax = fmaxf(amax, red[w]);
+  for (int w = 1; w < kMqThreads / 32; ++w) amax = fmaxf(amax, red[w]);
+  if (S > 1) {
+    if (threadIdx.x < S) {  // thread j publishes this CTA's amax into CTA j's slot [rank]
+      uint32_t local = smem_u32(cl_slots + rank), remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+      asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(remote), "f"(amax) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+    amax = cl_slots[0];
+    for (uint32_t j = 1; j < S; ++j) amax = fmaxf(amax, cl_slots[j]);
+  }
+  if (len <= 0) return;
   const float scale = amax / 448.0f;
-  if (threadIdx.x == 0) q_scales[b] = scale;
+  if (threadIdx.x == 0 && rank == 0) q_scales[b] = scale;
   const float inv = scale > 0.f ? 1.0f / scale : 0.f;
   uint8_t* qrow = q_out + static_cast<int64_t>(b) * q_stride;
-  for (int it = threadIdx.x; it < n4; it += 256) {  // each thread re-reads what it wrote itself
-    const uint2 pk = *reinterpret_cast<const uint2*>(row + it * 4);
-    const float2 a = unpack2<T>(pk.x), c = unpack2<T>(pk.y);
-    const float x0 = fmaxf(fminf(a.x * inv, 448.0f), -448.0f), x1 = fmaxf(fminf(a.y * inv, 448.0f), -448.0f);
-    const float x2 = fmaxf(fminf(c.x * inv, 448.0f), -448.0f), x3 = fmaxf(fminf(c.y * inv, 448.0f), -448.0f);
-    uint16_t lo, hi;
-    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(lo) : "f"(x1), "f"(x0));
-    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(hi) : "f"(x3), "f"(x2));
-    *reinterpret_cast<uint32_t*>(qrow + it * 4) = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+#pragma unroll
+  for (int k = 0; k < kMqMaxItems; ++k) {
+    const int it = i0 + threadIdx.x + k * kMqThreads;
+    if (it < i1) {
+      const float2 a = unpack2<T>(vals[k].x), c = unpack2<T>(vals[k].y);
+      const float x0 = fmaxf(fminf(a.x * inv, 448.0f), -448.0f), x1 = fmaxf(fminf(a.y * inv, 448.0f), -448.0f);
+      const float x2 = fmaxf(fminf(c.x * inv, 448.0f), -448.0f), x3 = fmaxf(fminf(c.y * inv, 448.0f), -448.0f);
+      uint16_t lo, hi;
+      asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(lo) : "f"(x1), "f"(x0));
+      asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(hi) : "f"(x3), "f"(x2));
+      *reinterpret_cast<uint32_t*>(qrow + it * 4) = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+    }
   }
 }
 
 template <typename T>
 static int launch_merge_quant(const DecodeParams& p, int Dv, int align, cudaStream_t st) {
-  const size_t smem = static_cast<size_t>(p.Hq) * Dv * sizeof(T);
-  B200_REQUIRE(smem <= 160 * 1024, "attn_merge_quant: row of %d x %d does not fit shared memory", p.Hq, Dv);
+  const int n4 = p.Hq * Dv / 4;
+  int S = ceil_div(n4, kMqThreads);  // one item per thread where the cluster limit allows it
+  if (S > 8) S = 8;
+  const int per_cta = ceil_div(n4, S);
+  B200_REQUIRE(per_cta <= kMqThreads * kMqMaxItems,
+               "attn_merge_quant: row of %d x %d is too long for one cluster", p.Hq, Dv);
   auto kern = attn_merge_quant_kernel<T>;
-  static size_t attr = 0;
-  if (smem > attr && smem > 48 * 1024) {
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      static_cast<int>(smem)));
-    attr = smem;
-  }
   {
     ScopedKernelTimer timer("attn_merge_quant", st);
-    B200_CUDA_OK(launch_kernel(kern, dim3(p.bs), dim3(256), smem, st, 1, pdl_family(p.bs, kPdlMerge),
-                               static_cast<const float*>(p.part_o), static_cast<const float*>(p.part_lse),
-                               static_cast<T*>(p.o), p.o_stride, 1, p.q_out, p.q_out_stride, p.q_scales,
-                               p.seq_lens, p.Hq, Dv, p.num_splits, align));
+    B200_CUDA_OK(launch_kernel(kern, dim3(p.bs * S), dim3(kMqThreads), 0, st, S,
+                               pdl_family(p.bs, kPdlMerge), static_cast<const float*>(p.part_o),
+                               static_cast<const float*>(p.part_lse), static_cast<T*>(p.o), p.o_stride,
+                               p.q_out, p.q_out_stride, p.q_scales, p.seq_lens, p.Hq, Dv, p.num_splits,
+                               align, per_cta));
   }
   B200_CHECK_LAUNCH("attn_merge_quant_kernel");
   return 0;

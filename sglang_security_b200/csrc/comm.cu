@@ -266,6 +266,10 @@ int b200_comm_all_reduce(void* comm, const void* in, void* out, int64_t numel, i
                static_cast<long long>(bytes), static_cast<unsigned long long>(c->dev.slot_bytes));
   const int64_t num_vec = bytes / 16;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  {
+    const int rc = comm_all_reduce_nvls(c, in, out, bytes, dtype, st);  // -1: not attached / too small
+    if (rc >= 0) return rc;
+  }
   const uint4* i4 = static_cast<const uint4*>(in);
   uint4* o4 = static_cast<uint4*>(out);
   if (bytes <= ll_max_bytes(c->dev.world) && static_cast<uint64_t>(2 * bytes) <= c->dev.slot_bytes) {

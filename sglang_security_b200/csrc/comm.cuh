@@ -157,6 +157,15 @@ __device__ __forceinline__ void comm_end(const CommDev& c, uint32_t e, uint32_t 
 struct Comm {
   CommDev dev;
   size_t buf_bytes;
+  // NVLS (comm_nvls.cu): this rank's slice of a multicast-bound allocation, mapped twice — uc = plain
+  // local view, mc = the multicast address whose loads are reduced inside the NVSwitch
+  uint8_t* nvls_uc = nullptr;
+  uint8_t* nvls_mc = nullptr;
+  size_t nvls_slot = 0;  // bytes of one of the two parity slots
 };
+
+// comm_nvls.cu: in-switch reduction path of b200_comm_all_reduce (returns -1 when it does not apply)
+int comm_all_reduce_nvls(const Comm* c, const void* in, void* out, int64_t bytes, int dtype,
+                         cudaStream_t st);
 
 }  // namespace b200

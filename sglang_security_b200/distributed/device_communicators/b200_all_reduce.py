@@ -13,6 +13,10 @@ The epoch counters live in device memory, so captured CUDA graphs replay without
 from __future__ import annotations
 
 import ctypes
+import os
+import socket
+import tempfile
+import uuid
 from typing import List, Optional
 
 import torch
@@ -64,6 +68,92 @@ class B200AllReduce:
         self.crossover = self.max_size if self.world_size <= 4 else min(self.max_size, 2 << 20)
         self.disabled = False
         dist.barrier(group=group)  # every rank has zeroed + mapped all buffers before first use
+        # in-switch reduction (NVLS) for the messages it wins on; silently absent where the fabric,
+        # the driver or the container does not offer multicast objects
+        self.nvls = False
+        self._nvls_buf = None
+        if os.environ.get("B200_COMM_NVLS", "1") != "0":
+            self._setup_nvls(group)
+            if self.nvls:
+                self.crossover = self.max_size  # the switch path keeps its lead up to the buffer limit
+
+    # -- NVLS ------------------------------------------------------------------------------------
+    def _all_ok(self, ok: bool, group) -> bool:
+        flags = [None] * self.world_size
+        dist.all_gather_object(flags, bool(ok), group=group)
+        return all(flags)
+
+    def _setup_nvls(self, group) -> None:
+        """Multicast object shared by the group (csrc/comm_nvls.cu): created on rank 0, its file
+        descriptor handed to the peers over a unix socket (SCM_RIGHTS), every rank adds its device,
+        binds its own physical memory and maps both views.  Every step is agreed on by all ranks,
+        so either all of them end up with NVLS or none does."""
+        lib = _lib.load()
+        size = 0
+        if lib.b200_nvls_supported():
+            size = int(lib.b200_nvls_buffer_bytes(self.world_size, 2 * self.max_size))
+        sizes = [None] * self.world_size
+        dist.all_gather_object(sizes, size, group=group)
+        if not all(sizes) or len(set(sizes)) != 1:
+            return
+        buf = ctypes.c_void_p()
+        path = [None]
+        srv = None
+        ok = True
+        if self.rank == 0:
+            fd = ctypes.c_int(-1)
+            ok = lib.b200_nvls_create(self.world_size, size, ctypes.byref(buf), ctypes.byref(fd)) == 0
+            if ok:
+                path[0] = os.path.join(tempfile.gettempdir(), f"b200_nvls_{os.getpid()}_{uuid.uuid4().hex}")
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path[0])
+                srv.listen(self.world_size)
+        src = dist.get_global_rank(group, 0) if group is not None else 0
+        dist.broadcast_object_list(path, src=src, group=group)
+        try:
+            if path[0] is None:
+                ok = False
+            elif self.rank == 0:
+                srv.settimeout(60)
+                for _ in range(self.world_size - 1):
+                    conn, _addr = srv.accept()
+                    socket.send_fds(conn, [b"fd"], [fd.value])
+                    conn.close()
+            else:
+                cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                cli.settimeout(60)
+                cli.connect(path[0])
+                _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
+                cli.close()
+                ok = len(fds) == 1 and lib.b200_nvls_import(fds[0], self.world_size, size,
+                                                            ctypes.byref(buf)) == 0
+                for f in fds:
+                    os.close(f)
+        except OSError:
+            ok = False
+        finally:
+            if srv is not None:
+                srv.close()
+                try:
+                    os.unlink(path[0])
+                except OSError:
+                    pass
+        if self.rank == 0 and ok:
+            os.close(fd.value)
+        with torch.cuda.device(self.device):
+            ok = self._all_ok(ok, group) and lib.b200_nvls_add_device(buf) == 0
+            ok = self._all_ok(ok, group)   # also the barrier between add_device and bind
+            uc, mc = ctypes.c_void_p(), ctypes.c_void_p()
+            ok = ok and lib.b200_nvls_bind(buf, ctypes.byref(uc), ctypes.byref(mc)) == 0
+            ok = self._all_ok(ok, group)
+            if ok:
+                ok = lib.b200_comm_attach_nvls(self.handle, buf) == 0
+            ok = self._all_ok(ok, group)
+        if ok:
+            self.nvls, self._nvls_buf = True, buf
+        elif buf.value:
+            lib.b200_comm_attach_nvls(self.handle, None)
+            lib.b200_nvls_free(buf)
 
     # -- buffers -------------------------------------------------------------------------------
     def create_shared_buffer(self, size_in_bytes: int,
@@ -132,6 +222,9 @@ class B200AllReduce:
                 dist.barrier(group=self.group)
             _lib.load().b200_comm_destroy(self.handle)
             self.handle = None
+            if self._nvls_buf is not None:
+                _lib.load().b200_nvls_free(self._nvls_buf)
+                self._nvls_buf, self.nvls = None, False
             self.free_shared_buffer()
             self.disabled = True
 

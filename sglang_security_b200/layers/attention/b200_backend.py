@@ -76,12 +76,12 @@ class B200AttnBackend(AttentionBackend):
         self._graph_max_bs = 0
         # fused decode tail (merge + optional o_proj input quantisation by the last CTA of a request)
         # fused_tail: False = split + merge kernels and a separate quantiser (the reference's launch
-        # structure).  True = the tail is fused: inside the split kernel (ticket counters) while the
-        # step is latency-bound, i.e. batch <= tail_in_kernel_max_bs, else as ONE merge+quantise launch
-        # (in-kernel tails cost the bandwidth-bound split kernel more than the launch they save:
-        # 8.93 vs 8.72 ms per step at batch 64 x 4k, profiles/r02_notes.md)
+        # structure).  True = ONE merge+quantise launch after the split kernel (a cluster of CTAs per
+        # request).  The in-kernel variant (ticket counters inside the split kernel, batch <=
+        # tail_in_kernel_max_bs) measured slower than both at every batch on B200
+        # (profiles/r02_decode_tail_modes.json) and is therefore off by default.
         self.fused_tail = os.environ.get("B200_ATTN_FUSED_TAIL", "1") != "0"
-        self.tail_in_kernel_max_bs = int(os.environ.get("B200_ATTN_TAIL_IN_KERNEL_MAX_BS", "16"))
+        self.tail_in_kernel_max_bs = int(os.environ.get("B200_ATTN_TAIL_IN_KERNEL_MAX_BS", "0"))
         self._tickets = torch.zeros(256 * (1 + self.num_head), dtype=torch.int32, device=self.device)
 
     def _ticket_buffer(self, bs: int) -> torch.Tensor:

@@ -181,8 +181,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _mp_worker(rank, world, port, out_dir):
+def _mp_worker(rank, world, port, out_dir, nvls=False):
     import torch.distributed as dist
+
+    os.environ["B200_COMM_NVLS"] = "1" if nvls else "0"
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -197,6 +199,12 @@ def _mp_worker(rank, world, port, out_dir):
     comm = ps.get_tp_custom_all_reduce()
     assert comm is not None and not comm.disabled
     g = torch.Generator().manual_seed(1234)  # same stream of numbers on every rank
+    if nvls:
+        _nvls_checks(rank, world, comm, ps, g, out_dir)
+        dist.barrier()
+        ps.destroy_model_parallel()
+        dist.destroy_process_group()
+        return
     for numel in [8, 4096, 64 * 4096, 256 * 8192]:
         xs = [(torch.randn(numel, generator=g) * 2).to(torch.bfloat16) for _ in range(world)]
         mine = xs[rank].cuda()
@@ -261,6 +269,61 @@ def _mp_worker(rank, world, port, out_dir):
     ps.destroy_model_parallel()
     open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     dist.destroy_process_group()
+
+
+def _nvls_checks(rank, world, comm, ps, g, out_dir):
+    """In-switch reduction (multimem.ld_reduce): fp32 accumulation inside the NVSwitch, one rounding,
+    but in the switch's own order -> compared with the fp32 sum at one 16-bit ulp, with NCCL, and
+    across ranks; CUDA-graph replays and both parities of the double buffer are exercised."""
+    import torch.distributed as dist
+
+    if not comm.nvls:   # fabric / driver / container without multicast support: recorded, not failed
+        open(os.path.join(out_dir, f"nvls_unavailable{rank}"), "w").write("x")
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+        return
+    for dtype, ulp in ((torch.bfloat16, 2 ** -8), (torch.float16, 2 ** -11), (torch.float32, 2 ** -22)):
+        for numel in [8192, 64 * 4096, 64 * 4096 + 8, 256 * 8192]:
+            for rep in range(3):   # epochs of both parities
+                xs = [(torch.randn(numel, generator=g) * 2).to(dtype) for _ in range(world)]
+                mine = xs[rank].cuda()
+                out = comm.all_reduce(mine)
+                exact = torch.stack([x.double() for x in xs]).sum(0)
+                err = (out.cpu().double() - exact).abs()
+                tol = ulp * exact.abs() * 1.01 + ulp * 2 * world   # one rounding (+ fp32 order noise)
+                assert (err <= tol).all(), (str(dtype), numel, rep, err.max().item())
+                outs = [torch.empty_like(out) for _ in range(world)]
+                dist.all_gather(outs, out)
+                same = all(torch.equal(outs[0], o) for o in outs)
+                if rank == 0 and not same:
+                    open(os.path.join(out_dir, "nvls_ranks_differ"), "a").write(f"{dtype} {numel}\n")
+    # CUDA graph: capture three all-reduces, replay twice, compare with an eager run
+    x = (torch.randn(64 * 4096, generator=g) * 2).to(torch.bfloat16).cuda()
+    ref = comm.all_reduce(comm.all_reduce(comm.all_reduce(x)))
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        comm.all_reduce(x)  # warm-up on the side stream
+        with torch.cuda.graph(graph, stream=s):
+            y = comm.all_reduce(comm.all_reduce(comm.all_reduce(x)))
+    torch.cuda.current_stream().wait_stream(s)
+    for _ in range(2):
+        graph.replay()
+        torch.cuda.synchronize()
+        torch.testing.assert_close(y.float(), ref.float(), rtol=2e-2, atol=1e-1 * world ** 3)
+    open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_nvls_all_reduce_multi_gpu(world, tmp_path):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_mp_worker, args=(world, _free_port(), str(tmp_path), True), nprocs=world, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
+    if (tmp_path / "nvls_unavailable0").exists():
+        pytest.skip("multicast objects are not available on this box (no NVLS)")
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])

@@ -48,12 +48,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--out", default="")
+    ap.add_argument("--ar-only", action="store_true", help="skip the row-parallel GEMM points")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
+    from sglang_security_b200 import _lib
     from sglang_security_b200.distributed import parallel_state as ps
     from sglang_security_b200.layers.quantization.fp8_kernel import fp8_scaled_mm
 
@@ -62,20 +64,27 @@ def main():
     assert comm is not None
     rows = []
     hidden = 4096
-    for tokens in [1, 8, 32, 64, 128, 256, 512]:
+    for tokens in [1, 2, 4, 8, 32, 64, 128, 256, 512]:
         x = torch.randn(tokens, hidden, device=dev).to(torch.bfloat16)
         out = torch.empty_like(x)
         y = x.clone()
+        us_nvls = None
+        if getattr(comm, "nvls", False):   # in-switch reduction vs the peer-memory kernels
+            us_nvls = timed_graph(lambda: comm.all_reduce(x, out=out), args.iters, dev)
+            _lib.load().b200_comm_attach_nvls(comm.handle, None)
         us_p2p = timed_graph(lambda: comm.all_reduce(x, out=out), args.iters, dev)
+        if getattr(comm, "nvls", False):
+            _lib.load().b200_comm_attach_nvls(comm.handle, comm._nvls_buf)
         us_nccl = timed_graph(lambda: dist.all_reduce(y), args.iters, dev)
         row = {"op": "all_reduce", "tp": world, "tokens": tokens, "bytes": x.numel() * 2,
-               "p2p_oneshot_us": round(us_p2p, 2), "nccl_us": round(us_nccl, 2)}
+               "p2p_oneshot_us": round(us_p2p, 2), "nccl_us": round(us_nccl, 2),
+               "nvls_us": None if us_nvls is None else round(us_nvls, 2)}
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
     # row-parallel GEMMs of Llama-3.1-8B (o_proj K = 4096/tp, down_proj K = 14336/tp), N = 4096
     g = torch.Generator(device=dev).manual_seed(rank)
-    for name, k_full in [("o_proj", 4096), ("down_proj", 14336)]:
+    for name, k_full in ([] if args.ar_only else [("o_proj", 4096), ("down_proj", 14336)]):
         k = k_full // world
         w = (torch.randn(hidden, k, device=dev, generator=g) * 0.5).to(FP8)
         sb = torch.rand(hidden, device=dev, generator=g) * 0.01 + 0.001
