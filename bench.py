@@ -454,10 +454,28 @@ def run_b200(args):
                      "nvls": bool(getattr(comm, "nvls", False)),
                      "row_parallel_message_bytes": bs * g.hidden * 2,
                      "all_reduces_per_step": 2 * layers + 1}
-    if rank != 0:
+    def teardown():
+        # A live CUDA graph that captured NCCL kernels keeps the communicator busy:
+        # destroy_process_group() then never returns (seen at N = 2: both ranks printed / finished
+        # and hung here).  Drop the graph first, then the communicators.
+        nonlocal graph
+        # belt and braces: the result line is out by now, so a teardown that still does not return
+        # within 45 s must not hold the launcher (and every other rank) forever
+        watchdog = threading.Timer(45.0, lambda: os._exit(0))
+        watchdog.daemon = True
+        watchdog.start()
+        graph = None
+        import gc
+
+        gc.collect()
+        torch.cuda.synchronize()
         if world > 1:
             destroy_model_parallel()
             dist.destroy_process_group()
+        watchdog.cancel()
+
+    if rank != 0:
+        teardown()
         return
 
     peak, peak_src = measured_peaks()
@@ -511,9 +529,7 @@ def run_b200(args):
             "clocks": clocks, "roofline": roofline, "roofline_step": roofline_step,
             "kernel_split_eager": split, "comm": comm_info, "cpu_baseline": cpu_baseline}
     print(json.dumps(line), flush=True)
-    if world > 1:
-        destroy_model_parallel()
-        dist.destroy_process_group()
+    teardown()
 
 
 def main():

@@ -72,7 +72,7 @@ class B200AllReduce:
         # the driver or the container does not offer multicast objects
         self.nvls = False
         self._nvls_buf = None
-        if os.environ.get("B200_COMM_NVLS", "1") != "0":
+        if os.environ.get("B200_COMM_NVLS", "0") == "1":   # opt-in until verified on the target fabric
             self._setup_nvls(group)
             if self.nvls:
                 self.crossover = self.max_size  # the switch path keeps its lead up to the buffer limit

@@ -79,6 +79,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--tune", action="store_true", help="cfg-2 point only, a few split counts")
+    ap.add_argument("--tp-shapes", action="store_true",
+                    help="per-rank head geometry of Llama-3.1-8B at TP 2/4/8 over a range of split counts")
     ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"])
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep_decode.json"))
     args = ap.parse_args()
@@ -98,7 +100,13 @@ def main():
                   for s in (0, 2, 3, 4, 5, 6, 8)]
         points.append(dict(bs=64, ctx=4096, hq=64, hkv=8, d=128, layers=4, slots_mode="random", splits=0))
         points.append(dict(bs=64, ctx=4096, hq=8, hkv=1, d=128, layers=16, slots_mode="random", splits=0))
-    if not args.quick and not args.tune:
+    if args.tp_shapes:
+        points = []
+        for hq, hkv in ((16, 4), (8, 2), (4, 1)):
+            for sp in (0, 2, 3, 4, 5, 6, 8, 9, 10, 12, 14, 16):
+                points.append(dict(bs=64, ctx=4096, hq=hq, hkv=hkv, d=128, layers=16, slots_mode="random",
+                                   splits=sp))
+    if not args.quick and not args.tune and not args.tp_shapes:
         points += [
             dict(bs=64, ctx=4096, hq=32, hkv=8, d=128, layers=4, slots_mode="random", splits=0, ragged=True),
             dict(bs=1, ctx=4096, hq=32, hkv=8, d=128, layers=8, slots_mode="random", splits=0),
