@@ -1,18 +1,23 @@
 #!/bin/bash
-# Scratch experiment list of the CURRENT GPU session.  This one: N-GPU check of the bench teardown fix
-# + NVLS test; every step under a short timeout.   gpurun --gpus N -- bash tools/gpu_exp.sh
+# Scratch experiment list of the CURRENT GPU session: source-level ncu of the mid-M FP8 GEMMs,
+# attention split sweep on the TP per-rank head geometries, bench with the cluster merge+quant.
 set -u
 out=gpurun_out
-tag=${GPU_TAG:-r02e}
-N=${GPU_N:-2}
+tag=${GPU_TAG:-r02f}
 mkdir -p $out
 t0=$(date +%s)
 stamp() { echo "== $1 (+$(( $(date +%s) - t0 )) s)"; }
-trun() { port=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port "$@"; }
-stamp "bench.py N=$N"
-timeout 200 bash -c "$(declare -f trun); N=$N; trun 29522 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n$N.json 2> $out/${tag}_bench_n$N.err; echo "rc=$?"; cut -c1-300 $out/${tag}_bench_n$N.json; grep -o '"kernel_split_eager.*' $out/${tag}_bench_n$N.json | cut -c1-1500; tail -2 $out/${tag}_bench_n$N.err | cut -c1-200
-stamp "nvls test"
-timeout 150 python -m pytest tests/test_comm_gpu.py -m gpu -q -x -k "nvls and $N" -rs > $out/${tag}_pytest_nvls.log 2>&1; echo "rc=$?"; tail -4 $out/${tag}_pytest_nvls.log | cut -c1-300
-stamp "reference arm N=$N"
-timeout 200 bash -c "$(declare -f trun); N=$N; trun 29524 bench.py --impl reference --gpus $N --steps 2 --warmup 1" > $out/${tag}_bench_ref_n$N.json 2> $out/${tag}_bench_ref_n$N.err; echo "rc=$?"; cut -c1-400 $out/${tag}_bench_ref_n$N.json
+NCU="ncu --set full --clock-control none --import-source on -f"
+stamp "ncu smallm M=64 s4"
+timeout 200 $NCU -k regex:fp8_gemm_smallm -s 4 -c 1 -o $out/${tag}_smallm_m64 python tools/prof_fp8.py 64 6144 4096 128 4 > $out/${tag}_ncu1.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu1.log | cut -c1-200
+stamp "ncu smallm M=32 s4"
+timeout 200 $NCU -k regex:fp8_gemm_smallm -s 4 -c 1 -o $out/${tag}_smallm_m32 python tools/prof_fp8.py 32 6144 4096 128 4 > $out/${tag}_ncu2.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu2.log | cut -c1-200
+stamp "ncu gemm_tn M=64"
+timeout 200 $NCU -k regex:gemm_tn -s 4 -c 1 -o $out/${tag}_gemmtn_m64 python tools/prof_fp8.py 64 6144 4096 > $out/${tag}_ncu3.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu3.log | cut -c1-200
+for f in smallm_m64 smallm_m32 gemmtn_m64; do python tools/ncu_summarize.py full $out/${tag}_$f.ncu-rep $out/${tag}_ncu_${f}_summary.json | grep -E "duration|dram__bytes_read.sum\"|issue_active|warps_active|registers|occupancy_limit|grid_size|tensor_cycles" ; done
+stamp "attention split sweep on TP shapes"
+timeout 400 python tools/sweep_decode.py --tp-shapes --out $out/${tag}_sweep_tp_shapes.json 2>&1 | cut -c1-250
+stamp "bench N=1 default / unfused"
+timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1.json
+B200_ATTN_FUSED_TAIL=0 timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1_unfused.json 2> $out/${tag}_bench_n1_unfused.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1_unfused.json
 stamp "done"
