@@ -893,6 +893,17 @@ int b200_attn_decode_num_splits(int bs, int Hkv, int group, int D, int64_t avg_l
   int64_t max_s = avg_len / (4 * align);
   if (max_s > 64) max_s = 64;
   if (max_s < 1) max_s = 1;
+  // Few kv heads per rank (tensor parallel): equal-length CTAs that all fit the resident slots at
+  // once finish together, while any overflow runs as a thin second wave.  Measured on the per-rank
+  // shapes of Llama-3.1-8B at TP 2/4/8, batch 64 x 4k (profiles/r02_sweep_decode_tp_shapes.json):
+  // the best split count is the LARGEST one whose CTAs fit one wave — 2 / 4 / 9 splits = 512 / 512 /
+  // 576 CTAs on 592 slots (90.8 / 50.7 / 29.9 us) against 93.9 / 56.4 / 35.3 us for the
+  // oversubscription rule below.
+  {
+    const int64_t s1 = slots / base;
+    if (s1 >= 2 && s1 <= max_s && static_cast<double>(base * s1) >= 0.85 * static_cast<double>(slots))
+      return static_cast<int>(s1);
+  }
   int best = static_cast<int>(max_s);
   for (int s = 1; s <= max_s; ++s) {
     if (static_cast<double>(base * s) >= kOver * static_cast<double>(slots)) {

@@ -108,6 +108,11 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_base));
   float* part = reinterpret_cast<float*>(smem_raw);  // [S * ceil(M/S)][128], aliases the W ring
+  // per-token activation scales, staged once by the epilogue warps: read inside the store loop
+  // they cost one serialised L2 round trip PER TOKEN (a load may not be hoisted above the previous
+  // token's output store) — 0.1-0.2 us per token, the whole M dependence of this kernel
+  // (profiles/r02_ncu_fp8_smallm_m64_source.md)
+  __shared__ float sa_s[MT];
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -225,6 +230,10 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
     griddep_wait();  // scales / bias / output buffers may belong to the previous kernel
     const int quarter = warp & 3;
     const int ch = quarter * 32 + lane;  // output channel within the tile (TMEM lane)
+    if (!BLK) {
+      if (ch < MT) sa_s[ch] = (p.sa && ch < p.M) ? __ldg(p.sa + static_cast<int64_t>(ch) * p.sa_stride) : 1.f;
+      named_bar_sync(2, 128);
+    }
     const int n = n_tile * 128 + ch;
     const bool n_ok = n < p.N;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -249,7 +258,7 @@ fp8_gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmap_w,
 
     auto finish = [&](int m, float v) {  // scales + bias + cast + store of one output element
       float sc = 1.f;
-      if (!BLK) sc = (p.sa ? __ldg(p.sa + static_cast<int64_t>(m) * p.sa_stride) : 1.f) * sbn;
+      if (!BLK) sc = sa_s[m] * sbn;
       if (!n_ok) return;
       const OutT o = from_float<OutT>(fmaf(v, sc, bn));
       if constexpr (AR) {

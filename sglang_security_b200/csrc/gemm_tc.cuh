@@ -125,6 +125,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                const GemmEpilogueParams ep) {
   using C = GemmCfg<KIND, BLOCK_N, STAGES>;
   extern __shared__ uint8_t smem_raw[];
+  // per-column scale and bias of the tile being finished (double-buffered per TMEM accumulator):
+  // staged BEFORE the accumulator wait.  Loading them inside the store loop serialised one L2/L1
+  // round trip per 8 columns — loads may not be hoisted above the preceding output stores (possible
+  // aliasing) — which the mid-M single-tile launches paid on their critical path.
+  __shared__ float sb_s[2][BLOCK_N];
+  __shared__ float bias_s[2][BLOCK_N];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B
   const uint32_t bars = smem_base + STAGES * C::STAGE_BYTES;
   auto full_bar = [&](int s) { return bars + 8u * s; };
@@ -259,8 +265,18 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const int n_blk = MC ? tile / (m_blocks / 2) : tile / m_blocks;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1u;
+      for (int cidx = quarter * 32 + lane; cidx < BLOCK_N; cidx += 128) {
+        const int col = n_blk * BLOCK_N + cidx;
+        const bool ok = col < ep.N;
+        sb_s[acc][cidx] = (ep.sb && ok) ? __ldg(ep.sb + static_cast<int64_t>(col) * ep.sb_stride) : 1.0f;
+        bias_s[acc][cidx] = (bias && ok) ? to_float<OutT>(bias[col]) : 0.0f;
+      }
+      named_bar_sync_gemm(1, 128);  // the four epilogue warps; a thread gets here only after it has
+                                    // finished the tile that used this buffer two tiles ago
       tc::mbar_wait(tfull_bar(acc), acc_phase);
       tc::tc_fence_after();
+      const float* sbt = sb_s[acc];
+      const float* bst = bias_s[acc];
       const int row = m_blk * C::BLOCK_M + quarter * 32 + lane;
       const bool row_ok = row < ep.M;
       const float sa = (ep.sa && row_ok) ? __ldg(ep.sa + static_cast<int64_t>(row) * ep.sa_stride)
@@ -307,13 +323,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               uint32_t packed[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                float s0 = sa, s1 = sa;
-                if (ep.sb) {
-                  s0 *= __ldg(ep.sb + static_cast<int64_t>(col0 + 2 * e) * ep.sb_stride);
-                  s1 *= __ldg(ep.sb + static_cast<int64_t>(col0 + 2 * e + 1) * ep.sb_stride);
-                }
-                const float b0 = bias ? to_float<OutT>(bias[col0 + 2 * e]) : 0.f;
-                const float b1 = bias ? to_float<OutT>(bias[col0 + 2 * e + 1]) : 0.f;
+                const float s0 = sa * sbt[g * 8 + 2 * e], s1 = sa * sbt[g * 8 + 2 * e + 1];
+                const float b0 = bst[g * 8 + 2 * e], b1 = bst[g * 8 + 2 * e + 1];
                 packed[e] = pack_out2<OutT>(fmaf(sum[2 * e], s0, b0), fmaf(sum[2 * e + 1], s1, b1));
               }
               *reinterpret_cast<uint4*>(orow + col0) =
@@ -322,9 +333,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 if (col0 + j >= ep.N) break;
-                float sc = sa;
-                if (ep.sb) sc *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
-                const float bb = bias ? to_float<OutT>(bias[col0 + j]) : 0.f;
+                const float sc = sa * sbt[g * 8 + j];
+                const float bb = bst[g * 8 + j];
                 orow[col0 + j] = from_float<OutT>(fmaf(sum[j], sc, bb));
               }
             }
@@ -351,16 +361,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               for (int e = 0; e < 4; ++e) {
                 const int j = v * 8 + e * 2;
                 float x0 = __uint_as_float(r[j]), x1 = __uint_as_float(r[j + 1]);
-                float s0 = sa, s1 = sa;
-                if (ep.sb) {
-                  s0 *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
-                  s1 *= __ldg(ep.sb + static_cast<int64_t>(col0 + j + 1) * ep.sb_stride);
-                }
-                float b0 = 0.f, b1 = 0.f;
-                if (bias) {
-                  b0 = to_float<OutT>(bias[col0 + j]);
-                  b1 = to_float<OutT>(bias[col0 + j + 1]);
-                }
+                const float s0 = sa * sbt[c * 32 + j], s1 = sa * sbt[c * 32 + j + 1];
+                const float b0 = bst[c * 32 + j], b1 = bst[c * 32 + j + 1];
                 packed[e] = pack_out2<OutT>(fmaf(x0, s0, b0), fmaf(x1, s1, b1));
               }
               *reinterpret_cast<uint4*>(orow + col0 + v * 8) =
@@ -370,9 +372,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               if (col0 + j >= ep.N) break;
-              float s = sa;
-              if (ep.sb) s *= __ldg(ep.sb + static_cast<int64_t>(col0 + j) * ep.sb_stride);
-              const float b = bias ? to_float<OutT>(bias[col0 + j]) : 0.f;
+              const float s = sa * sbt[c * 32 + j];
+              const float b = bst[c * 32 + j];
               orow[col0 + j] = from_float<OutT>(fmaf(__uint_as_float(r[j]), s, b));
             }
           }

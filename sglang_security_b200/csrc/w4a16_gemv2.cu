@@ -372,9 +372,13 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
     const int cshift = 31 - __clz(cpr);
     T* o = static_cast<T*>(p.out);
     const T* bias = static_cast<const T*>(p.bias);
+    // kG2Threads is a multiple of cpr: a thread keeps the same column for all of its items, so its
+    // bias is loaded once (inside the loop the load would wait behind the previous output store)
+    const int c = static_cast<int>(rank) * cpr + (threadIdx.x & (cpr - 1));
+    const int n = n_grp * 128 + c;
+    const float bias_n = (bias && n < p.N) ? to_float<T>(bias[n]) : 0.f;
     for (int item = threadIdx.x; item < p.M * cpr; item += kG2Threads) {
-      const int m = item >> cshift, c = static_cast<int>(rank) * cpr + (item & (cpr - 1));
-      const int n = n_grp * 128 + c;
+      const int m = item >> cshift;
       const uint32_t local = sbase + p.part_off + (m * 128 + c) * 4;
       float sum = 0.f;
       if (S == 1) {
@@ -388,10 +392,7 @@ w4a16_gemv2_kernel(const Gemv2Params p) {
           sum += v;
         }
       }
-      if (n < p.N) {
-        if (bias) sum += to_float<T>(bias[n]);
-        o[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(sum);
-      }
+      if (n < p.N) o[static_cast<int64_t>(m) * p.ldc + n] = from_float<T>(sum + bias_n);
     }
   }
   if (S > 1) g2_cluster_sync();  // peers may still be reading this CTA's partial tile

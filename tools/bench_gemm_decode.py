@@ -22,7 +22,10 @@ from sglang_security_b200.layers.quantization.fp8_kernel import (fp8_blockwise_s
 
 FP8 = torch.float8_e4m3fn
 SHAPES = {"llama8b": [(6144, 4096), (4096, 4096), (28672, 4096), (4096, 14336)],
-          "llama70b_tp8": [(1280, 8192), (8192, 1024), (7168, 8192), (8192, 3584)]}
+          "llama70b_tp8": [(1280, 8192), (8192, 1024), (7168, 8192), (8192, 3584)],
+          "llama8b_tp2": [(3072, 4096), (4096, 2048), (14336, 4096), (4096, 7168)],
+          "llama8b_tp4": [(1536, 4096), (4096, 1024), (7168, 4096), (4096, 3584)],
+          "llama8b_tp8": [(768, 4096), (4096, 512), (3584, 4096), (4096, 1792)]}
 
 
 def graph_time(fns, reps):

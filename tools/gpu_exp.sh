@@ -1,23 +1,23 @@
 #!/bin/bash
-# Scratch experiment list of the CURRENT GPU session: source-level ncu of the mid-M FP8 GEMMs,
-# attention split sweep on the TP per-rank head geometries, bench with the cluster merge+quant.
+# Scratch experiment list of the CURRENT GPU session: after staging the epilogue scales in shared memory.
 set -u
 out=gpurun_out
-tag=${GPU_TAG:-r02f}
+tag=${GPU_TAG:-r02g}
 mkdir -p $out
 t0=$(date +%s)
 stamp() { echo "== $1 (+$(( $(date +%s) - t0 )) s)"; }
-NCU="ncu --set full --clock-control none --import-source on -f"
-stamp "ncu smallm M=64 s4"
-timeout 200 $NCU -k regex:fp8_gemm_smallm -s 4 -c 1 -o $out/${tag}_smallm_m64 python tools/prof_fp8.py 64 6144 4096 128 4 > $out/${tag}_ncu1.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu1.log | cut -c1-200
-stamp "ncu smallm M=32 s4"
-timeout 200 $NCU -k regex:fp8_gemm_smallm -s 4 -c 1 -o $out/${tag}_smallm_m32 python tools/prof_fp8.py 32 6144 4096 128 4 > $out/${tag}_ncu2.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu2.log | cut -c1-200
-stamp "ncu gemm_tn M=64"
-timeout 200 $NCU -k regex:gemm_tn -s 4 -c 1 -o $out/${tag}_gemmtn_m64 python tools/prof_fp8.py 64 6144 4096 > $out/${tag}_ncu3.log 2>&1; echo "rc=$?"; tail -1 $out/${tag}_ncu3.log | cut -c1-200
-for f in smallm_m64 smallm_m32 gemmtn_m64; do python tools/ncu_summarize.py full $out/${tag}_$f.ncu-rep $out/${tag}_ncu_${f}_summary.json | grep -E "duration|dram__bytes_read.sum\"|issue_active|warps_active|registers|occupancy_limit|grid_size|tensor_cycles" ; done
-stamp "attention split sweep on TP shapes"
-timeout 400 python tools/sweep_decode.py --tp-shapes --out $out/${tag}_sweep_tp_shapes.json 2>&1 | cut -c1-250
-stamp "bench N=1 default / unfused"
-timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1.json
-B200_ATTN_FUSED_TAIL=0 timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1_unfused.json 2> $out/${tag}_bench_n1_unfused.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1_unfused.json
+stamp "pytest gpu"
+timeout 900 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -6 $out/${tag}_pytest_gpu.log | cut -c1-300
+stamp "mid-M sweep llama8b"
+timeout 400 python tools/bench_gemm_decode.py --ms 16,32,48,64,96,128 --variants auto,big,s1,s2,s4,s8 --kinds rowcol --out $out/${tag}_gemm_midm.json 2>&1 | cut -c1-420
+for tp in tp2 tp4 tp8; do
+stamp "mid-M sweep llama8b_$tp"
+timeout 300 python tools/bench_gemm_decode.py --model llama8b_$tp --ms 32,64,128 --variants auto,big,s1,s2,s4,s8 --kinds rowcol --out $out/${tag}_gemm_midm_$tp.json 2>&1 | cut -c1-420
+done
+stamp "bench N=1"
+timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1.json; grep -o '"kernel_split_eager.*"comm"' $out/${tag}_bench_n1.json | cut -c1-900
+stamp "bench N=1 --splits 1"
+timeout 300 python bench.py --no-cpu-baseline --splits 1 > $out/${tag}_bench_n1_s1.json 2> $out/${tag}_bench_n1_s1.err; echo "rc=$?"; cut -c1-330 $out/${tag}_bench_n1_s1.json; grep -o '"attn_decode_split": {[^}]*}' $out/${tag}_bench_n1_s1.json
+stamp "w4a16 gemv2 (bias hoist does not apply here; sanity)"
+timeout 300 python tools/bench_w4a16.py --tp tp2 --ms 1,8,16 --skip-ref --out $out/${tag}_w4a16.json 2>&1 | cut -c1-330
 stamp "done"
