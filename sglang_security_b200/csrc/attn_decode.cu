@@ -901,7 +901,9 @@ int b200_attn_decode_num_splits(int bs, int Hkv, int group, int D, int64_t avg_l
   // oversubscription rule below.
   {
     const int64_t s1 = slots / base;
-    if (s1 >= 2 && s1 <= max_s && static_cast<double>(base * s1) >= 0.85 * static_cast<double>(slots))
+    // (s1 == 1, the 512 CTAs of the whole-model bench shape: 170.4 us and no merge launch against
+    //  174.4 us + merge with two splits, profiles/r02_bench_n1.json)
+    if (s1 >= 1 && s1 <= max_s && static_cast<double>(base * s1) >= 0.85 * static_cast<double>(slots))
       return static_cast<int>(s1);
   }
   int best = static_cast<int>(max_s);

@@ -205,3 +205,26 @@ class B200DecodeStep:
         if self.tp_size > 1:
             logits = tensor_model_parallel_all_gather(logits)
         out_token_ids.copy_(logits.argmax(-1))
+
+    def forward_extend(self, input_ids, positions, forward_batch, last_index, out_token_ids) -> None:
+        """One extend (prefill over a cached radix prefix) step: `input_ids` / `positions` hold the
+        NEW tokens of all requests back to back, `forward_batch` is in EXTEND mode
+        (extend_seq_lens / extend_prefix_lens / out_cache_loc filled), `last_index` [bs] = row of every
+        request's last new token.  Only those rows go through the lm_head, as in
+        LogitsProcessor.forward (layers/logits_processor.py:236-260)."""
+        if self.tp_size > 1:
+            local = input_ids - self.tp_rank * self.vocab_per_rank
+            outside = (local < 0) | (local >= self.vocab_per_rank)
+            h = self.embed[local.masked_fill(outside, 0)]
+            h.masked_fill_(outside.unsqueeze(-1), 0)
+            h = tensor_model_parallel_all_reduce(h)
+        else:
+            h = self.embed[input_ids]
+        residual = None
+        for L in self.layers:
+            h, residual = L(positions, h, forward_batch, residual)
+        h, _ = self.final_norm(h, residual)
+        logits = gemm_16bit(h[last_index].contiguous(), self.lm_head)
+        if self.tp_size > 1:
+            logits = tensor_model_parallel_all_gather(logits)
+        out_token_ids.copy_(logits.argmax(-1))

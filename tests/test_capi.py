@@ -47,7 +47,11 @@ def test_host_side_helpers_need_no_gpu(lib_path):
     assert lib.b200_attn_decode_workspace_bytes(64, 32, 128, 1) == 0
     assert lib.b200_attn_decode_workspace_bytes(64, 32, 128, 4) == 64 * 32 * 4 * (128 + 1) * 4
     s = lib.b200_attn_decode_num_splits(64, 8, 4, 128, 4096, 148)
-    assert 1 <= s <= 64
+    assert s == 1   # 512 CTAs fit the 592 resident slots: one balanced wave, no merge
+    # per-rank head counts of TP 2 / 4 / 8: the largest split count that still fits one wave
+    assert lib.b200_attn_decode_num_splits(64, 4, 4, 128, 4096, 148) == 2
+    assert lib.b200_attn_decode_num_splits(64, 2, 4, 128, 4096, 148) == 4
+    assert lib.b200_attn_decode_num_splits(64, 1, 4, 128, 4096, 148) == 9
     assert lib.b200_attn_decode_num_splits(1, 8, 4, 128, 100, 148) == 1
     assert lib.b200_attn_decode_split_align(128, 4) == 48  # 3 warps x 16-token tiles
 
