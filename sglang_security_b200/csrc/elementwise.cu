@@ -520,9 +520,11 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
   using namespace b200;
   if (M == 0) return 0;
   B200_REQUIRE(x && (out || q), "b200_silu_and_mul: null pointer");
-  B200_REQUIRE(d > 0 && d % 8 == 0 && d <= kRowThreads * 8 * kMaxIters,
+  // a CTA holds at most kRowThreads * kMaxIters vectors of a row in registers; longer rows (Qwen2.5-32B
+  // without TP: d = 27648) are split over a cluster of up to 8 CTAs
+  B200_REQUIRE(d > 0 && d % 8 == 0 && d <= 8 * kRowThreads * 8 * kMaxIters,
                "b200_silu_and_mul: d must be a multiple of 8 and <= %d (d=%d)",
-               kRowThreads * 8 * kMaxIters, d);
+               8 * kRowThreads * 8 * kMaxIters, d);
   B200_REQUIRE(quant_mode >= 0 && quant_mode <= 2 && (quant_mode == 0 || (q && scales)),
                "b200_silu_and_mul: bad quant_mode %d / missing q or scales", quant_mode);
   B200_REQUIRE(quant_mode != 2 || d % 128 == 0, "b200_silu_and_mul: group quant needs d %% 128 == 0");
@@ -546,6 +548,7 @@ int b200_silu_and_mul(const void* x, int64_t ldx, void* out, int64_t ldo, void* 
     }();
     int S = 8;
     while (S > 1 && (M * S > target || nvec < S * kRowThreads)) S >>= 1;
+    while (ceil_div(ceil_div(nvec, S), 16) * 16 > kRowThreads * kMaxIters) S <<= 1;  // register window
     const int per = ceil_div(ceil_div(nvec, S), 16) * 16;  // 128-groups stay inside one CTA
     if (dtype == B200_BF16)
       B200_CUDA_OK(launch_kernel(silu_mul_kernel<__nv_bfloat16>, dim3(M * S), dim3(kRowThreads), 0, st,

@@ -62,7 +62,10 @@ struct SmallMCfg {
   // (gate_up M = 1: 20.7 -> 19.6 us = 6.0 TB/s, 92 % of the HBM peak; down 11.1 us) but -7 % on
   // qkv / o, whose short K slices then hold too few blocks, so the launcher picks it by weight size.
   // The block-scaled variant needs one TMEM buffer per 128 K and keeps KS = 1.
-  static constexpr int KS = (!BLK && MT <= 32) ? KSUB : 1;
+  // MT = 16 only: the MT = 32 instance with 32 KiB ring blocks sits at the two-CTAs-per-SM shared
+  // memory limit and fell to one CTA per SM once the epilogue's scale staging was added (gate_up
+  // M = 32: 21.5 -> 26.8 us, down 13.3 -> 25.7 us, profiles/r02_bench_gemm_midm.json)
+  static constexpr int KS = (!BLK && MT <= 16) ? KSUB : 1;
   static constexpr int W_SUB = 128 * 128, X_SUB = MT * 128;
   static constexpr int W_BYTES = KS * W_SUB;
   static constexpr int X_BYTES = KS * X_SUB;
@@ -445,7 +448,7 @@ int launch_smallm_ks(const void* x, int64_t ldx, const void* w, int64_t ldw, Sma
 template <int MT, bool BLK, typename OutT, bool AR>
 int launch_smallm(const void* x, int64_t ldx, const void* w, int64_t ldw, const SmallMParams& p,
                   cudaStream_t st, const char* timer_name) {
-  if constexpr (!BLK && MT <= 32 && !AR) {
+  if constexpr (!BLK && MT <= 16 && !AR) {
     // 256-K ring blocks for weights of 48 MB and more (gate_up, down_proj of the named models)
     if (static_cast<int64_t>(p.N) * p.K >= (48ll << 20))
       return launch_smallm_ks<MT, BLK, OutT, AR, 2>(x, ldx, w, ldw, p, st, timer_name);

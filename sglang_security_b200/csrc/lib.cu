@@ -23,7 +23,9 @@ std::atomic<int> g_pdl_on{pdl_default()};
 int pdl_max_tokens() {
   static int v = [] {
     const char* e = std::getenv("B200_PDL_MAX_M");
-    return (e && *e) ? std::atoi(e) : 32;
+    // 64: re-measured in round 2 on the whole-model bench (batch 64 x 4k: 8.112 ms with PDL up to 64
+    // or 256 tokens against 8.245 ms with the round-1 limit of 32, profiles/r02_bench_pdl.json)
+    return (e && *e) ? std::atoi(e) : 64;
   }();
   return v;
 }

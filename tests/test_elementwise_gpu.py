@@ -83,7 +83,8 @@ def test_rmsnorm_seeded_and_fused_quant(m, k, dtype):
 
 
 @pytest.mark.parametrize("m,d", [(1, 14336), (64, 14336), (5, 256), (33, 4864), (130, 3584),
-                                 (3, 4864), (16, 14336), (20, 5120), (2, 16384), (4, 2056)])
+                                 (3, 4864), (16, 14336), (20, 5120), (2, 16384), (4, 2056),
+                                 (3, 27648), (200, 27648)])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 def test_silu_and_mul(m, d, dtype):
     from sglang_security_b200.layers.activation import SiluAndMul

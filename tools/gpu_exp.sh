@@ -1,38 +1,37 @@
 #!/bin/bash
-# Scratch experiment list of the CURRENT GPU session: PDL retest at batch 64, whole-model sweeps for the
-# DESIGN tables, cfg-4 (AWQ) and cfg-5 (SafeKV multi-turn) tools on one GPU, round-2 ncu captures.
+# Scratch experiment list of the CURRENT GPU session: the 8-GPU session (every second costs 8x).
+#   gpurun --gpus 8 -- bash tools/gpu_exp.sh
 set -u
 out=gpurun_out
-tag=${GPU_TAG:-r02h}
+tag=${GPU_TAG:-r02i}
+N=${GPU_N:-8}
 mkdir -p $out
 t0=$(date +%s)
 stamp() { echo "== $1 (+$(( $(date +%s) - t0 )) s)"; }
+trun() { n=$1; port=$2; shift 2; python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port "$@"; }
 brief() { python - "$1" <<'PY'
 import json,sys
 try:
-    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
-    print("  ", sys.argv[1].split("/")[-1], "ms/step", round(d["ms_per_step"],3), "tok/s", round(d["value"]), "e2e", round(d["e2e"]["value"]), "splits", d["config"]["num_kv_splits"], "attn us", d["roofline"]["us_per_launch"], "frac", round(d["roofline"]["frac"],3), "step frac", round(d["roofline_step"]["frac"],3))
+    d=json.loads([l for l in open(sys.argv[1]).read().strip().splitlines() if l.startswith("{")][-1])
+    ks=d.get("kernel_split_eager",{})
+    print("  ", sys.argv[1].split("/")[-1], "ms/step", round(d["ms_per_step"],3), "tok/s", round(d["value"]), "e2e", round(d["e2e"]["value"]), "splits", d["config"]["num_kv_splits"], "attn us", d["roofline"]["us_per_launch"], "comm", d.get("comm"))
+    print("     ", {k:(v["launches_per_step"], v["us_per_launch"]) for k,v in ks.items()})
 except Exception as e: print("ERR", sys.argv[1], e)
 PY
 }
-stamp "bench default"
-timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "rc=$?"; brief $out/${tag}_bench_n1.json
-for pm in 64 256; do
-stamp "bench PDL up to $pm tokens"
-B200_PDL_MAX_M=$pm timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_pdl$pm.json 2> $out/${tag}_bench_pdl$pm.err; echo "rc=$?"; brief $out/${tag}_bench_pdl$pm.json
-done
-stamp "whole-model sweep (bf16 KV)"
-timeout 400 python tools/bench_decode_model.py --bs 1,8,16,32,64,128,256 --ctx 1024,4096 --out $out/${tag}_decode_model_llama8b_fp8_tp1.json 2>&1 | cut -c1-230
-stamp "whole-model sweep (fp8 KV)"
-timeout 400 python tools/bench_decode_model.py --bs 1,16,64,128 --ctx 1024,4096 --kv-dtype fp8 --out $out/${tag}_decode_model_llama8b_fp8_tp1_kvfp8.json 2>&1 | cut -c1-230
-stamp "cfg 4: Qwen2.5-32B AWQ on one GPU"
-timeout 500 python tools/bench_decode_model.py --model qwen2.5-32b --quant awq --bs 1,8,16,64 --ctx 1024 --out $out/${tag}_decode_model_qwen32b_awq_tp1.json 2>&1 | cut -c1-330
-stamp "cfg 5 tool on one GPU (Llama-3.1-8B)"
-timeout 400 python tools/bench_safekv_multiturn.py --users 16 --turns 3 --out $out/${tag}_safekv_llama8b_tp1.json 2>&1 | tail -5 | cut -c1-500
-stamp "ncu launch list"
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $out/${tag}_launches.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_launch.log 2>&1; echo "rc=$?"
-python tools/ncu_summarize.py launches $out/${tag}_launches.csv $out/${tag}_ncu_launches.json | grep -v "torch:" | tail -14 | cut -c1-200
-stamp "ncu full attention"
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:attn_decode_mma -s 40 -c 2 -f -o $out/${tag}_decode_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1; echo "rc=$?"
-python tools/ncu_summarize.py full $out/${tag}_decode_full.ncu-rep $out/${tag}_ncu_decode_full_summary.json | grep -E "duration|dram__bytes|registers|issue_active" | head -8
+nvidia-smi topo -m > $out/${tag}_topo.txt 2>&1
+stamp "all-reduce latency N=$N (NVLS on)"
+B200_COMM_NVLS=1 timeout 120 bash -c "$(declare -f trun); trun $N 29521 tools/bench_allreduce.py --ar-only --out $out/${tag}_bench_allreduce_tp$N.json" 2>&1 | grep "^{" | cut -c1-200
+stamp "bench.py N=$N"
+timeout 150 bash -c "$(declare -f trun); trun $N 29522 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n$N.json 2> $out/${tag}_bench_n$N.err; echo "rc=$?"; brief $out/${tag}_bench_n$N.json; tail -2 $out/${tag}_bench_n$N.err | cut -c1-200
+stamp "bench.py N=$N NVLS"
+B200_COMM_NVLS=1 timeout 150 bash -c "$(declare -f trun); trun $N 29523 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_nvls.json 2> $out/${tag}_bench_n${N}_nvls.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_nvls.json
+stamp "bench.py N=$N PDL up to 512 tokens"
+B200_PDL_MAX_M=512 timeout 150 bash -c "$(declare -f trun); trun $N 29524 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_pdl.json 2> $out/${tag}_bench_n${N}_pdl.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_pdl.json
+stamp "bench.py N=4"
+timeout 150 bash -c "$(declare -f trun); trun 4 29525 bench.py --gpus 4 --no-cpu-baseline" > $out/${tag}_bench_n4.json 2> $out/${tag}_bench_n4.err; echo "rc=$?"; brief $out/${tag}_bench_n4.json
+stamp "nvls + ipc tests world $N"
+B200_COMM_NVLS=1 timeout 200 python -m pytest tests/test_comm_gpu.py -m gpu -q -x -k "multi_gpu and $N" -rs > $out/${tag}_pytest_comm.log 2>&1; echo "rc=$?"; tail -4 $out/${tag}_pytest_comm.log | cut -c1-300
+stamp "cfg 5: Llama-3.1-70B FP8 TP=$N, SafeKV multi-turn"
+timeout 300 bash -c "$(declare -f trun); trun $N 29526 tools/bench_safekv_multiturn.py --users 32 --turns 3 --decode-steps 4 --out $out/${tag}_safekv_llama70b_tp$N.json" 2>&1 | grep "^{" | cut -c1-600
 stamp "done"
