@@ -20,18 +20,18 @@ except Exception as e: print("ERR", sys.argv[1], e)
 PY
 }
 nvidia-smi topo -m > $out/${tag}_topo.txt 2>&1
+stamp "bench.py N=$N"
+timeout 100 bash -c "$(declare -f trun); trun $N 29522 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n$N.json 2> $out/${tag}_bench_n$N.err; echo "rc=$?"; brief $out/${tag}_bench_n$N.json; tail -2 $out/${tag}_bench_n$N.err | cut -c1-200
 stamp "all-reduce latency N=$N (NVLS on)"
 B200_COMM_NVLS=1 timeout 120 bash -c "$(declare -f trun); trun $N 29521 tools/bench_allreduce.py --ar-only --out $out/${tag}_bench_allreduce_tp$N.json" 2>&1 | grep "^{" | cut -c1-200
-stamp "bench.py N=$N"
-timeout 150 bash -c "$(declare -f trun); trun $N 29522 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n$N.json 2> $out/${tag}_bench_n$N.err; echo "rc=$?"; brief $out/${tag}_bench_n$N.json; tail -2 $out/${tag}_bench_n$N.err | cut -c1-200
 stamp "bench.py N=$N NVLS"
-B200_COMM_NVLS=1 timeout 150 bash -c "$(declare -f trun); trun $N 29523 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_nvls.json 2> $out/${tag}_bench_n${N}_nvls.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_nvls.json
+B200_COMM_NVLS=1 timeout 100 bash -c "$(declare -f trun); trun $N 29523 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_nvls.json 2> $out/${tag}_bench_n${N}_nvls.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_nvls.json
 stamp "bench.py N=$N PDL up to 512 tokens"
-B200_PDL_MAX_M=512 timeout 150 bash -c "$(declare -f trun); trun $N 29524 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_pdl.json 2> $out/${tag}_bench_n${N}_pdl.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_pdl.json
+B200_PDL_MAX_M=512 timeout 100 bash -c "$(declare -f trun); trun $N 29524 bench.py --gpus $N --no-cpu-baseline" > $out/${tag}_bench_n${N}_pdl.json 2> $out/${tag}_bench_n${N}_pdl.err; echo "rc=$?"; brief $out/${tag}_bench_n${N}_pdl.json
 stamp "bench.py N=4"
-timeout 150 bash -c "$(declare -f trun); trun 4 29525 bench.py --gpus 4 --no-cpu-baseline" > $out/${tag}_bench_n4.json 2> $out/${tag}_bench_n4.err; echo "rc=$?"; brief $out/${tag}_bench_n4.json
+timeout 100 bash -c "$(declare -f trun); trun 4 29525 bench.py --gpus 4 --no-cpu-baseline" > $out/${tag}_bench_n4.json 2> $out/${tag}_bench_n4.err; echo "rc=$?"; brief $out/${tag}_bench_n4.json
 stamp "nvls + ipc tests world $N"
-B200_COMM_NVLS=1 timeout 200 python -m pytest tests/test_comm_gpu.py -m gpu -q -x -k "multi_gpu and $N" -rs > $out/${tag}_pytest_comm.log 2>&1; echo "rc=$?"; tail -4 $out/${tag}_pytest_comm.log | cut -c1-300
+B200_COMM_NVLS=1 timeout 120 python -m pytest tests/test_comm_gpu.py -m gpu -q -x -k "multi_gpu and $N" -rs > $out/${tag}_pytest_comm.log 2>&1; echo "rc=$?"; tail -4 $out/${tag}_pytest_comm.log | cut -c1-300
 stamp "cfg 5: Llama-3.1-70B FP8 TP=$N, SafeKV multi-turn"
-timeout 300 bash -c "$(declare -f trun); trun $N 29526 tools/bench_safekv_multiturn.py --users 32 --turns 3 --decode-steps 4 --out $out/${tag}_safekv_llama70b_tp$N.json" 2>&1 | grep "^{" | cut -c1-600
+timeout 150 bash -c "$(declare -f trun); trun $N 29526 tools/bench_safekv_multiturn.py --users 32 --turns 3 --decode-steps 4 --out $out/${tag}_safekv_llama70b_tp$N.json" 2>&1 | grep "^{" | cut -c1-600
 stamp "done"
