@@ -414,7 +414,7 @@ int b200_comm_fuse_config(int max_m);
  *   b200_nvls_add_device(buf)                  every rank; host barrier; then
  *   b200_nvls_bind(buf, &uc, &mc)              every rank: own physical memory bound + both views mapped
  *   b200_comm_attach_nvls(comm, buf)           b200_comm_all_reduce now uses the switch for messages of
- *                                              B200_COMM_NVLS_MIN (16 KiB) .. size / 2 bytes
+ *                                              B200_COMM_NVLS_MIN (128 KiB) .. size / 2 bytes
  *   b200_nvls_free(buf)                                                                           */
 int b200_nvls_supported(void);
 size_t b200_nvls_buffer_bytes(int world, size_t bytes);

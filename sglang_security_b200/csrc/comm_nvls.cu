@@ -125,7 +125,9 @@ all_reduce_nvls_kernel(const CommDev c, uint8_t* __restrict__ uc, const uint8_t*
 static int64_t nvls_min_bytes() {
   static int64_t v = [] {
     const char* e = std::getenv("B200_COMM_NVLS_MIN");
-    return (e && *e) ? std::atoll(e) : static_cast<int64_t>(16 << 10);
+    // 128 KiB: below that the LL protocol's single NVLink trip wins (TP 8: 9.4 vs 10.7 us at 64 KiB,
+    // 14.9 vs 12.9 us at 256 KiB; profiles/r02_bench_allreduce_tp8.json)
+    return (e && *e) ? std::atoll(e) : static_cast<int64_t>(128 << 10);
   }();
   return v;
 }
@@ -323,7 +325,7 @@ int b200_nvls_free(void* buf) {
 }
 
 /* Hand a bound NVLS buffer to a communicator: from now on b200_comm_all_reduce reduces messages of
- * B200_COMM_NVLS_MIN (default 16 KiB) .. size / 2 bytes inside the switch. */
+ * B200_COMM_NVLS_MIN (default 128 KiB) .. size / 2 bytes inside the switch. */
 int b200_comm_attach_nvls(void* comm, void* nvls_buf) {
   using namespace b200;
   B200_REQUIRE(comm, "b200_comm_attach_nvls: null communicator");

@@ -133,6 +133,22 @@ __device__ __forceinline__ float cluster_max(float v, float* slots /* [8] shared
   return r;
 }
 
+// sum over the cluster in rank order (the same value on every CTA, deterministic for a given S)
+__device__ __forceinline__ float cluster_sum(float v, float* slots /* [8] shared */) {
+  const uint32_t S = cluster_size();
+  if (S == 1) return v;
+  const uint32_t rank = cluster_rank();
+  if (threadIdx.x < S) {
+    uint32_t local = static_cast<uint32_t>(__cvta_generic_to_shared(slots + rank)), remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(local), "r"(threadIdx.x));
+    asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(remote), "f"(v) : "memory");
+  }
+  cluster_barrier();
+  float r = slots[0];
+  for (uint32_t j = 1; j < S; ++j) r += slots[j];
+  return r;
+}
+
 template <typename T>
 __device__ __forceinline__ void emit_row(const float (&y)[kMaxIters][8], int nvec, int m,
                                          const RowOut& o, float* red, int i0 = 0,
@@ -209,19 +225,26 @@ __device__ __forceinline__ void emit_row(const float (&y)[kMaxIters][8], int nve
 // ---- (residual +) RMSNorm -----------------------------------------------------------------------
 // layernorm.py:95-104: x32 = x (+ residual); residual' = T(x32); var = mean(x32^2);
 //                      y = T( (x32 * rsqrt(var + eps)) * weight )
+// Small token counts: a row is split over a cluster of gridDim.x / M CTAs (`per` vectors each); the sum
+// of squares is combined over distributed shared memory in rank order, the per-token amax as a maximum.
 template <typename T>
 __global__ void __launch_bounds__(kRowThreads)
 rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, int64_t ldr,
-               const T* __restrict__ weight, int K, float eps, RowOut o) {
+               const T* __restrict__ weight, int K, float eps, int per, RowOut o) {
   __shared__ float red[32];
-  const int m = blockIdx.x;
-  const int nvec = K / 8;
+  __shared__ float cl_sum[8];
+  __shared__ float cl_max[8];
+  const uint32_t S = cluster_size();
+  if (S > 1) cluster_barrier();  // every CTA of the cluster runs before any remote store is issued
+  const int m = blockIdx.x / S;
+  const int i0 = static_cast<int>(cluster_rank()) * per;
+  const int nvec = min(K / 8, i0 + per);
   // the norm weight does not depend on the previous kernel: fetch it before the dependency wait so
   // its latency overlaps the predecessor's tail instead of following the reduction
   uint4 wraw[kMaxIters];
 #pragma unroll
   for (int it = 0; it < kMaxIters; ++it) {
-    const int i = threadIdx.x + it * kRowThreads;
+    const int i = i0 + threadIdx.x + it * kRowThreads;
     wraw[it] = i < nvec ? __ldg(reinterpret_cast<const uint4*>(weight + i * 8)) : make_uint4(0, 0, 0, 0);
   }
   griddep_wait();
@@ -232,7 +255,7 @@ rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, i
   float ss = 0.f;
 #pragma unroll
   for (int it = 0; it < kMaxIters; ++it) {
-    const int i = threadIdx.x + it * kRowThreads;
+    const int i = i0 + threadIdx.x + it * kRowThreads;
     if (i < nvec) {
       ld8(xrow + i * 8, y[it]);
       if (rrow) {
@@ -247,10 +270,11 @@ rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, i
     }
   }
   ss = block_reduce<false>(ss, red);
+  ss = cluster_sum(ss, cl_sum);
   const float inv = 1.0f / sqrtf(__fadd_rn(ss / static_cast<float>(K), eps));
 #pragma unroll
   for (int it = 0; it < kMaxIters; ++it) {
-    const int i = threadIdx.x + it * kRowThreads;
+    const int i = i0 + threadIdx.x + it * kRowThreads;
     if (i < nvec) {
       const uint32_t wr[4] = {wraw[it].x, wraw[it].y, wraw[it].z, wraw[it].w};
 #pragma unroll
@@ -261,7 +285,7 @@ rmsnorm_kernel(const T* __restrict__ x, int64_t ldx, T* __restrict__ residual, i
       }
     }
   }
-  emit_row<T>(y, nvec, m, o, red);
+  emit_row<T>(y, nvec, m, o, red, i0, S > 1 ? cl_max : nullptr);
 }
 
 // ---- SiLU(gate) * up ------------------------------------------------------------------------------
@@ -500,15 +524,27 @@ int b200_rmsnorm(const void* x, int64_t ldx, void* residual, int64_t ldr, const 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   {
     ScopedKernelTimer timer("rmsnorm", st);
+    // cluster size: spread few rows over more SMs (a 4096-wide row on one CTA is a chain of dependent
+    // latencies: 6.3 us at 64 tokens in the whole-model launch list) while every CTA keeps >= 128 vectors;
+    // B200_RMSNORM_TARGET_CTAS overrides the CTA count aimed for (default 2 per SM, 0 = never split)
+    static const int target = [] {
+      const char* e = std::getenv("B200_RMSNORM_TARGET_CTAS");
+      return (e && *e) ? std::atoi(e) : 2 * device_sm_count();
+    }();
+    const int nvec = K / 8;
+    int S = 8;
+    while (S > 1 && (M * S > target || nvec < S * 128)) S >>= 1;
+    const int per = ceil_div(ceil_div(nvec, S), 16) * 16;  // 128-groups stay inside one CTA
     if (dtype == B200_BF16)
-      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__nv_bfloat16>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
-                                 static_cast<const __nv_bfloat16*>(x), ldx,
+      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__nv_bfloat16>, dim3(M * S), dim3(kRowThreads), 0, st, S,
+                                 pdl_family(M, kPdlRow), static_cast<const __nv_bfloat16*>(x), ldx,
                                  static_cast<__nv_bfloat16*>(residual), ldr,
-                                 static_cast<const __nv_bfloat16*>(weight), K, eps, o));
+                                 static_cast<const __nv_bfloat16*>(weight), K, eps, per, o));
     else
-      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__half>, dim3(M), dim3(kRowThreads), 0, st, 1, pdl_family(M, kPdlRow),
-                                 static_cast<const __half*>(x), ldx, static_cast<__half*>(residual),
-                                 ldr, static_cast<const __half*>(weight), K, eps, o));
+      B200_CUDA_OK(launch_kernel(rmsnorm_kernel<__half>, dim3(M * S), dim3(kRowThreads), 0, st, S,
+                                 pdl_family(M, kPdlRow), static_cast<const __half*>(x), ldx,
+                                 static_cast<__half*>(residual), ldr, static_cast<const __half*>(weight), K,
+                                 eps, per, o));
   }
   B200_CHECK_LAUNCH("rmsnorm_kernel");
   return 0;

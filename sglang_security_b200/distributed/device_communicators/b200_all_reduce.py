@@ -72,7 +72,11 @@ class B200AllReduce:
         # the driver or the container does not offer multicast objects
         self.nvls = False
         self._nvls_buf = None
-        if os.environ.get("B200_COMM_NVLS", "0") == "1":   # opt-in until verified on the target fabric
+        # Default: on for groups of 8 (measured on 8 x B200, profiles/r02_bench_allreduce_tp8.json:
+        # 15.9 vs 24.3 us at 512 KiB, whole-model TP 8 decode 3.86 vs 4.67 ms per step), off below
+        # (TP 2: the LL kernel is 2x faster).  B200_COMM_NVLS=1 / 0 forces it on / off.
+        want = os.environ.get("B200_COMM_NVLS", "")
+        if want == "1" or (want != "0" and self.world_size >= 8):
             self._setup_nvls(group)
             if self.nvls:
                 self.crossover = self.max_size  # the switch path keeps its lead up to the buffer limit
