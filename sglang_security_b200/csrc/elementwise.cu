@@ -524,12 +524,13 @@ int b200_rmsnorm(const void* x, int64_t ldx, void* residual, int64_t ldr, const 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   {
     ScopedKernelTimer timer("rmsnorm", st);
-    // cluster size: spread few rows over more SMs (a 4096-wide row on one CTA is a chain of dependent
-    // latencies: 6.3 us at 64 tokens in the whole-model launch list) while every CTA keeps >= 128 vectors;
-    // B200_RMSNORM_TARGET_CTAS overrides the CTA count aimed for (default 2 per SM, 0 = never split)
+    // Optional cluster split of a row (B200_RMSNORM_TARGET_CTAS = CTA count to aim for).  Off by default:
+    // unlike SiLU*mul (56 exp + divide per thread on a 14336-wide row) a 4096-wide norm row is a short
+    // chain of dependent latencies that the extra cluster barriers only lengthen — measured 10.65 vs
+    // 9.74 us per launch, whole step 8.238 vs 8.232 ms at 64 tokens (profiles/r02_bench_rmsnorm_split.json).
     static const int target = [] {
       const char* e = std::getenv("B200_RMSNORM_TARGET_CTAS");
-      return (e && *e) ? std::atoi(e) : 2 * device_sm_count();
+      return (e && *e) ? std::atoi(e) : 0;
     }();
     const int nvec = K / 8;
     int S = 8;
