@@ -57,7 +57,9 @@ fp8_quant_per_token_kernel(const T* __restrict__ x, int64_t ldx, uint8_t* __rest
   constexpr bool STATIC = MODE == 1;
   __shared__ float red[32];
   griddep_wait();
-  griddep_launch_dependents();
+  // MODE 2 quantises WEIGHTS at load time: its consumers (the GEMMs) prefetch their weight operand
+  // before their own dependency wait, so this kernel must not release them early
+  if (MODE != 2) griddep_launch_dependents();
   const int m = blockIdx.x;
   const T* row = x + m * ldx;
   uint8_t* out = q + m * ldq;

@@ -178,6 +178,26 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if (MC) cluster_sync_all();  // the peer's barriers are initialised before anything targets them
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // Programmatic dependent launch: everything a previous kernel may have written (activations,
+  // scales, outputs) is touched only after griddep_wait().  The B operand is a WEIGHT in every use of
+  // this kernel, so the producer thread puts the first ring stages of its first tile's B in flight
+  // before it waits: the TMA fill then overlaps the previous kernel's tail (the mid-M launches are
+  // a chain of fixed latencies, profiles/r02_ncu_fp8_smallm_m64_source.md).
+  int b_prefetched = 0;
+  if (warp == 0 && lane == 0) {
+    if (!MC && item0 < num_items) {
+      const int tile = item0 / S, ks = item0 - tile * S;
+      const int n_blk = tile / m_blocks;
+      const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
+      const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
+      b_prefetched = min(STAGES, kb1 - kb0);
+      for (int i = 0; i < b_prefetched; ++i) {
+        tc::mbar_arrive_expect_tx(full_bar(i), C::STAGE_BYTES);
+        tc::tma_load_2d(smem_base + i * C::STAGE_BYTES + C::A_BYTES, &tmap_b, full_bar(i),
+                        (kb0 + i) * C::BLOCK_K, n_blk * BLOCK_N);
+      }
+    }
+  }
   griddep_wait();  // activations / scales come from the previous kernel
   griddep_launch_dependents();
 
@@ -193,9 +213,18 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const int kb0 = S > 1 ? ks * ep.kb_per_split : 0;
         const int kb1 = S > 1 ? min(num_kb, kb0 + ep.kb_per_split) : num_kb;
         for (int kb = kb0; kb < kb1; ++kb) {
+          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+          if (b_prefetched > 0) {  // first stages of the first tile: B is already on its way
+            --b_prefetched;
+            tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * C::BLOCK_K, m_blk * C::BLOCK_M);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
+            continue;
+          }
           tc::mbar_wait(empty_bar(stage), phase ^ 1u);
           tc::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
-          const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
           tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * C::BLOCK_K, m_blk * C::BLOCK_M);
           if (MC)
             tc::tma_load_2d_mcast(sa + C::A_BYTES + mc_rank * (C::B_BYTES / 2), &tmap_b,
