@@ -23,9 +23,10 @@ std::atomic<int> g_pdl_on{pdl_default()};
 int pdl_max_tokens() {
   static int v = [] {
     const char* e = std::getenv("B200_PDL_MAX_M");
-    // 64: re-measured in round 2 on the whole-model bench (batch 64 x 4k: 8.112 ms with PDL up to 64
-    // or 256 tokens against 8.245 ms with the round-1 limit of 32, profiles/r02_bench_pdl.json)
-    return (e && *e) ? std::atoi(e) : 64;
+    // 512: re-measured in round 2 on the whole-model decode step (profiles/r02_bench_pdl.json): batch
+    // 64 x 4k 8.11 ms with PDL against 8.25 ms without; batch 128 / 256 @ 1k 5.99 / 9.62 ms against
+    // 6.20 / 9.84 ms with a limit of 64 tokens (round 1 had measured a loss from 64 tokens on)
+    return (e && *e) ? std::atoi(e) : 512;
   }();
   return v;
 }
