@@ -263,6 +263,12 @@ int b200_fp8_gemm_block128(const void* a, int64_t lda, const void* b, int64_t ld
 int b200_gemm_16bit(const void* x, int64_t ldx, const void* w, int64_t ldw, const void* bias,
                     void* out, int64_t ldc, int M, int N, int K, int dtype, void* stream);
 
+/* ---- greedy sampling ----------------------------------------------------------------------- */
+/* out[m] = index of the FIRST maximum of row m of x [M, V] (bf16 / f16, row stride ldx elements):
+ * torch.argmax(logits, -1) of Sampler.forward (python/sglang/srt/layers/sampler.py:60-66), with a row
+ * spread over a cluster of CTAs instead of torch's single CTA per row.                           */
+int b200_argmax_rows(const void* x, int64_t ldx, int64_t* out, int M, int V, int dtype, void* stream);
+
 /* ---- INT4 weight-only (W4A16): AWQ / GPTQ ------------------------------------- */
 /* Bit-exact AWQ dequant with the reference layouts (replaces sgl_kernel.awq_dequantize,
  * sgl-kernel/csrc/gemm/awq_kernel.cu:126-219): qweight [K, N/8] int32, qzeros [K/g, N/8] int32,

@@ -111,6 +111,7 @@ _SIGNATURES = {
     "b200_fp8_gemm_block128_ar": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                                           c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
                                           c_int64, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_argmax_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_gemm_16bit": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
                                 c_int, c_int, c_int, c_int, c_void_p]),
     "b200_w4a16_gemv": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,

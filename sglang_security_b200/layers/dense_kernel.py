@@ -33,3 +33,16 @@ def gemm_16bit(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tenso
                                      _lib.dtype_code(x.dtype), _lib.current_stream())
     _lib.check(rc, "b200_gemm_16bit")
     return out.reshape(x.shape[:-1] + (n,))
+
+
+def argmax_rows(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """torch.argmax(logits, -1) for CUDA bf16/f16 [M, V] logits (first index of the maximum) -> int64 [M]."""
+    if not logits.is_cuda or logits.dim() != 2 or logits.stride(-1) != 1:
+        raise _lib.B200Error("argmax_rows: logits must be a 2-D CUDA tensor with contiguous rows")
+    m, v = logits.shape
+    if out is None:
+        out = torch.empty((m,), dtype=torch.int64, device=logits.device)
+    rc = _lib.load().b200_argmax_rows(logits.data_ptr(), logits.stride(0), out.data_ptr(), m, v,
+                                      _lib.dtype_code(logits.dtype), _lib.current_stream())
+    _lib.check(rc, "b200_argmax_rows")
+    return out

@@ -29,7 +29,7 @@ import torch.nn.functional as F
 from ..distributed.parallel_state import (tensor_model_parallel_all_gather,
                                           tensor_model_parallel_all_reduce)
 from ..layers.attention.b200_backend import B200AttnBackend
-from ..layers.dense_kernel import gemm_16bit
+from ..layers.dense_kernel import argmax_rows, gemm_16bit
 from ..layers.layernorm import RMSNorm
 from ..layers.rotary_embedding import RotaryEmbedding
 from ..mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
@@ -204,7 +204,7 @@ class B200DecodeStep:
         logits = F.linear(h, self.lm_head) if _LM_HEAD_LIBRARY else gemm_16bit(h, self.lm_head)
         if self.tp_size > 1:
             logits = tensor_model_parallel_all_gather(logits)
-        out_token_ids.copy_(logits.argmax(-1))
+        argmax_rows(logits.reshape(-1, logits.shape[-1]), out_token_ids)   # greedy sampling, in-tree kernel
 
     def forward_extend(self, input_ids, positions, forward_batch, last_index, out_token_ids) -> None:
         """One extend (prefill over a cached radix prefix) step: `input_ids` / `positions` hold the
@@ -227,4 +227,4 @@ class B200DecodeStep:
         logits = gemm_16bit(h[last_index].contiguous(), self.lm_head)
         if self.tp_size > 1:
             logits = tensor_model_parallel_all_gather(logits)
-        out_token_ids.copy_(logits.argmax(-1))
+        argmax_rows(logits.reshape(-1, logits.shape[-1]), out_token_ids)   # greedy sampling, in-tree kernel

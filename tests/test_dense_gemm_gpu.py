@@ -46,3 +46,19 @@ def test_unquantized_linear_method_runs_the_in_tree_kernel():
     assert b"gemm_tn kind=1" in load().b200_last_variant()
     ref = torch.nn.functional.linear(x.float(), layer.weight.float(), layer.bias.float())
     assert (out.float() - ref).abs().max() <= 2 ** -6 * ref.abs().max()
+
+
+@pytest.mark.parametrize("m,v", [(1, 128256), (64, 128256), (3, 1000), (700, 32000), (5, 151936), (2, 8)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_argmax_rows_equals_torch_argmax(m, v, dtype):
+    """Greedy sampling kernel: first index of the row maximum, ties included (bf16 logits tie often)."""
+    from sglang_security_b200.layers.dense_kernel import argmax_rows
+
+    g = torch.Generator(device="cuda").manual_seed(m * 7 + v)
+    x = torch.randn((m, v), device="cuda", generator=g).to(dtype)
+    x[0, : min(v, 5)] = x[0].max()            # a tie at the very start of a row
+    if v > 300:
+        x[-1, 299] = x[-1, v - 1] = x[-1].max() + 1  # a tie across CTAs of the cluster
+    assert torch.equal(argmax_rows(x), torch.argmax(x, dim=-1))
+    xs = torch.randn((m, v + 8), device="cuda", generator=g).to(dtype)[:, 3:v + 3]   # unaligned rows
+    assert torch.equal(argmax_rows(xs), torch.argmax(xs, dim=-1))

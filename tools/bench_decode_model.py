@@ -100,7 +100,7 @@ def main():
     from sglang_security_b200 import _lib
     from sglang_security_b200.distributed.parallel_state import initialize_model_parallel
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
-    from sglang_security_b200.layers.dense_kernel import gemm_16bit
+    from sglang_security_b200.layers.dense_kernel import argmax_rows, gemm_16bit
     from sglang_security_b200.layers.layernorm import RMSNorm
     from sglang_security_b200.layers.rotary_embedding import RotaryEmbedding
     from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
@@ -186,7 +186,7 @@ def main():
                 h, residual = L(positions, h, fb, residual)
             h, _ = final_norm(h, residual)
             logits = gemm_16bit(h, lm_head)
-            out_tok.copy_(logits.argmax(-1))
+            argmax_rows(logits, out_tok)
 
         backend.init_forward_metadata(fb)
         n0 = _lib.load().b200_launch_count()

@@ -1,15 +1,18 @@
 #!/bin/bash
-# Scratch experiment list of the CURRENT GPU session: large-M FP8 GEMM re-measure after the epilogue
-# staging, FP8-KV decode attention with the single-wave split rule, then the full verification.
+# Scratch experiment list of the CURRENT GPU session: in-tree argmax kernel; batch-1 launch list.
 set -u
 out=gpurun_out
+tag=${GPU_TAG:-r02k}
 mkdir -p $out
 t0=$(date +%s)
 stamp() { echo "== $1 (+$(( $(date +%s) - t0 )) s)"; }
-stamp "large-M FP8 GEMM vs cuBLASLt"
-timeout 400 python tools/bench_gemm.py --ms 512,2048,8192 --out $out/r02_bench_gemm_large.json 2>&1 | cut -c1-600 | tail -16
-stamp "fp8-KV decode attention"
-timeout 300 python tools/sweep_decode.py --tune --kv-dtype fp8 --out $out/r02_sweep_decode_fp8kv.json 2>&1 | cut -c1-260
-stamp "verify"
-bash tools/gpu_session.sh verify
+stamp "pytest gpu"
+timeout 900 python -m pytest tests -m gpu -q > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 $out/${tag}_pytest_gpu.log | cut -c1-300
+stamp "bench"
+timeout 300 python bench.py --no-cpu-baseline > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err; echo "rc=$?"; grep -o '"ms_per_step": [0-9.]*' $out/${tag}_bench_n1.json | head -2
+stamp "small batches"
+timeout 300 python tools/bench_decode_model.py --bs 1,8,32 --ctx 1024,4096 --out $out/${tag}_decode_small.json 2>&1 | grep -o '"bs": [0-9]*, "ctx": [0-9]*\|"ms_per_step": [0-9.]*' | paste - -
+stamp "ncu launch list batch 1"
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $out/${tag}_launches_bs1.csv python tools/bench_decode_model.py --bs 1 --ctx 1024 --steps 1 > $out/${tag}_ncu_bs1.log 2>&1; echo "rc=$?"
+python tools/ncu_summarize.py launches $out/${tag}_launches_bs1.csv $out/${tag}_ncu_decode_model_bs1_launches.json | grep -v "torch:" | tail -16 | cut -c1-220
 stamp "done"
