@@ -230,7 +230,12 @@ int b200_fp8_quant_group128(const void* x, int64_t ldx, void* q, int64_t ldq, fl
 /* Replaces sgl_kernel.fp8_scaled_mm (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1071-1146):
  *   out[M,N] = (A[M,K] . B[N,K]^T) * sa[m*sa_stride] * sb[n*sb_stride] (+ bias[n])
  * A e4m3 row-major (lda), B e4m3 stored [N,K] K-contiguous (ldb) — i.e. the reference's
- * column-major [K,N] weight view; sa/sb fp32 (stride 0 = per-tensor); bias/out bf16 or f16.      */
+ * column-major [K,N] weight view; sa/sb fp32 (stride 0 = per-tensor); bias/out bf16 or f16.
+ * B is treated as a WEIGHT: with programmatic dependent launch (b200_set_pdl, on by default) the
+ * kernels start fetching B before the previous kernel of the stream has finished, so B must not be
+ * produced by a b200 kernel launched immediately before on the same stream (torch kernels and the
+ * library's load-time quantisers never release their dependents early, so they are safe).  The same
+ * holds for the weight operand of b200_fp8_gemm_block128, b200_gemm_16bit and the W4A16 GEMV.     */
 int b200_fp8_gemm_rowcol(const void* a, int64_t lda, const void* b, int64_t ldb, const float* sa,
                          int sa_stride, const float* sb, int sb_stride, const void* bias,
                          void* out, int64_t ldc, int M, int N, int K, int out_dtype,

@@ -133,7 +133,7 @@ class B200AllReduce:
                                                             ctypes.byref(buf)) == 0
                 for f in fds:
                     os.close(f)
-        except OSError:
+        except Exception:  # noqa: BLE001 - any failure of the fd hand-off just means "no NVLS"
             ok = False
         finally:
             if srv is not None:
