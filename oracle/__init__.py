@@ -13,5 +13,8 @@ Pinning status (details in DESIGN.md §3):
       python-loop definition (test/srt/test_create_kvindices.py:40-49).
   FP8 quant / GEMM, AWQ   : restatements of the torch references inside the reference's tests
       (file:line in each function); pinned by fixtures generated from those test files.
+  scheduler index kernels : pinned — get_last_loc / compute_position by the reference's torch twins,
+      alloc_extend / alloc_decode by the reference's own Triton kernels run in Triton's CPU
+      interpreter (tests/golden/sched_index.pt, sched_alloc.pt).
   GPTQ                    : parity unpinned (arithmetic lives in vllm 0.8.4, absent).
 """

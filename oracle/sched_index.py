@@ -11,9 +11,10 @@ Python-loop restatements of the reference's scheduler-side index kernels:
 
 Pinned by: tests/golden/sched_index.pt = outputs of the reference's own get_last_loc_torch and
 compute_position_torch (source extracted unmodified from the reference files by
-oracle/gen_golden_sched_index.py).  The allocator kernels have no torch twin in the reference
-(its tests only check served outputs, test/srt/test_page_size.py) -> restated, "parity unpinned",
-cross-checked by invariants (unique slots, page alignment, continuation of the last page).
+oracle/gen_golden_sched_index.py), and tests/golden/sched_alloc.pt = outputs of the reference's own
+Triton allocator kernels (source extracted unmodified, executed on CPU tensors through Triton's
+interpreter by oracle/gen_golden_alloc.py), plus invariants (unique slots, page alignment,
+continuation of the last page).
 """
 from __future__ import annotations
 

@@ -159,3 +159,26 @@ def test_decode_attention_on_paged_slots(page):
     assert torch.equal(kb.view(torch.int16), k_ref.view(torch.int16))
     st = harness.error_stats(o, o_ref)
     assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, st
+
+
+def test_alloc_kernels_match_reference_triton_goldens():
+    """b200_alloc_extend / b200_alloc_decode against tests/golden/sched_alloc.pt = the outputs of the
+    reference's own Triton allocator kernels (oracle/gen_golden_alloc.py), bit-exact, including the
+    pages consumed."""
+    import os
+
+    from sglang_security_b200.mem_cache.paged_allocator import PagedTokenToKVPoolAllocator
+
+    cases = torch.load(os.path.join(os.path.dirname(__file__), "golden", "sched_alloc.pt"))
+    for c in cases:
+        page = c["page_size"]
+        alloc = PagedTokenToKVPoolAllocator(8192 * page, page, torch.bfloat16, "cuda")
+        alloc.free_pages = c["free_pages"].cuda()
+        out = alloc.alloc_extend(c["prefix_lens"].cuda(), c["seq_lens"].cuda(), c["last_loc"].cuda(),
+                                 int(c["extend_sum_extend_lens"]))
+        assert torch.equal(out.cpu(), c["extend_out_indices"]), page
+        assert torch.equal(alloc.free_pages.cpu(), c["free_pages"][c["extend_num_new_pages"]:])
+        assert torch.equal(alloc.free_pages.cpu(), c["decode_free_pages"])
+        dec = alloc.alloc_decode(c["decode_seq_lens"].cuda(), c["decode_last_loc"].cuda())
+        assert torch.equal(dec.cpu(), c["decode_out_indices"]), page
+        assert alloc.free_pages.numel() == c["decode_free_pages"].numel() - c["decode_num_new_pages"]

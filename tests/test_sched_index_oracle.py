@@ -35,3 +35,25 @@ def test_alloc_oracle_invariants():
     dec, used_d = O.alloc_decode_oracle(torch.tensor([17, 18, 33]), torch.tensor([15, 16 * 9, 16 * 7 + 15]),
                                         torch.tensor([70, 71]), page)
     assert dec.tolist() == [70 * 16, 16 * 9 + 1, 71 * 16] and used_d == 2
+
+
+ALLOC_GOLD = os.path.join(os.path.dirname(__file__), "golden", "sched_alloc.pt")
+
+
+def test_alloc_oracle_matches_reference_triton_kernels():
+    """tests/golden/sched_alloc.pt = outputs of the reference's OWN alloc_extend_kernel /
+    alloc_decode_kernel (paged_allocator.py:29-155), run unmodified through Triton's CPU interpreter
+    (oracle/gen_golden_alloc.py): page sizes 1 / 16 / 32 / 64, empty and page-aligned prefixes,
+    extends ending on a page boundary, one-token extends."""
+    cases = torch.load(ALLOC_GOLD)
+    assert len(cases) >= 6
+    for c in cases:
+        page = c["page_size"]
+        out, used = O.alloc_extend_oracle(c["prefix_lens"], c["seq_lens"], c["last_loc"], c["free_pages"], page)
+        assert torch.equal(out, c["extend_out_indices"]), page
+        assert used == c["extend_num_new_pages"]
+        assert int((c["seq_lens"] - c["prefix_lens"]).sum()) == c["extend_sum_extend_lens"]
+        dec, used_d = O.alloc_decode_oracle(c["decode_seq_lens"], c["decode_last_loc"],
+                                            c["decode_free_pages"], page)
+        assert torch.equal(dec, c["decode_out_indices"]), page
+        assert used_d == c["decode_num_new_pages"]
