@@ -182,3 +182,32 @@ def test_alloc_kernels_match_reference_triton_goldens():
         dec = alloc.alloc_decode(c["decode_seq_lens"].cuda(), c["decode_last_loc"].cuda())
         assert torch.equal(dec.cpu(), c["decode_out_indices"]), page
         assert alloc.free_pages.numel() == c["decode_free_pages"].numel() - c["decode_num_new_pages"]
+
+
+def test_index_kernels_match_reference_triton_goldens():
+    """b200_kv_indices / b200_write_req_to_token against the outputs of the reference's own Triton kernels
+    (tests/golden/triton_index.pt, oracle/gen_golden_triton_index.py): bit-exact."""
+    import os
+
+    from sglang_security_b200 import _lib
+    from sglang_security_b200.mem_cache.paged_allocator import write_req_to_token_pool
+
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "triton_index.pt"))
+    lib = _lib.load()
+    for c in gold["kv_indices"]:
+        rtt = c["req_to_token"].cuda()
+        rpi = c["req_pool_indices"].to(torch.int64).cuda()
+        lens = c["lens"].to(torch.int64).cuda()
+        indptr = c["kv_indptr"].cuda()
+        start = None if c["kv_start"] is None else c["kv_start"].cuda()
+        out = torch.full((int(c["kv_indptr"][-1]),), -1, dtype=torch.int32, device="cuda")
+        rc = lib.b200_kv_indices(rtt.data_ptr(), rtt.stride(0), rpi.data_ptr(), lens.data_ptr(),
+                                 indptr.data_ptr(), _lib.ptr(start), out.data_ptr(), rpi.numel(),
+                                 _lib.current_stream())
+        _lib.check(rc, "b200_kv_indices")
+        assert torch.equal(out.cpu(), c["kv_indices"])
+    for c in gold["write_req_to_token"]:
+        table = c["req_to_token_before"].cuda()
+        write_req_to_token_pool(table, c["req_pool_indices"].cuda(), c["pre_lens"].cuda(), c["seq_lens"].cuda(),
+                                c["extend_lens"].cuda(), c["out_cache_loc"].cuda())
+        assert torch.equal(table.cpu(), c["req_to_token_after"])

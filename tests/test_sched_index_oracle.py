@@ -57,3 +57,19 @@ def test_alloc_oracle_matches_reference_triton_kernels():
                                             c["decode_free_pages"], page)
         assert torch.equal(dec, c["decode_out_indices"]), page
         assert used_d == c["decode_num_new_pages"]
+
+
+def test_index_oracles_match_reference_triton_kernels():
+    """tests/golden/triton_index.pt = outputs of the reference's own create_flashinfer_kv_indices_triton
+    (layers/attention/utils.py:5-41) and write_req_to_token_pool_triton (schedule_batch.py:1789-1823) run
+    through Triton's CPU interpreter (oracle/gen_golden_triton_index.py)."""
+    from oracle.pools import kv_indices_oracle
+
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "triton_index.pt"))
+    for c in gold["kv_indices"]:
+        indptr, flat = kv_indices_oracle(c["req_to_token"], c["req_pool_indices"], c["lens"], c["kv_start"])
+        assert torch.equal(indptr, c["kv_indptr"]) and torch.equal(flat, c["kv_indices"])
+    for c in gold["write_req_to_token"]:
+        got = O.write_req_to_token_oracle(c["req_to_token_before"].clone(), c["req_pool_indices"], c["pre_lens"],
+                                          c["seq_lens"], c["extend_lens"], c["out_cache_loc"])
+        assert torch.equal(got, c["req_to_token_after"])
