@@ -104,14 +104,18 @@ class B200AllReduce:
         path = [None]
         srv = None
         ok = True
+        fd = ctypes.c_int(-1)
         if self.rank == 0:
-            fd = ctypes.c_int(-1)
             ok = lib.b200_nvls_create(self.world_size, size, ctypes.byref(buf), ctypes.byref(fd)) == 0
             if ok:
-                path[0] = os.path.join(tempfile.gettempdir(), f"b200_nvls_{os.getpid()}_{uuid.uuid4().hex}")
-                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                srv.bind(path[0])
-                srv.listen(self.world_size)
+                try:   # a failure here must still reach the broadcast below (path stays None)
+                    name = os.path.join(tempfile.gettempdir(), f"b200_nvls_{os.getpid()}_{uuid.uuid4().hex}")
+                    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                    srv.bind(name)
+                    srv.listen(self.world_size)
+                    path[0] = name
+                except OSError:
+                    ok = False
         src = dist.get_global_rank(group, 0) if group is not None else 0
         dist.broadcast_object_list(path, src=src, group=group)
         try:
@@ -138,12 +142,13 @@ class B200AllReduce:
         finally:
             if srv is not None:
                 srv.close()
-                try:
-                    os.unlink(path[0])
-                except OSError:
-                    pass
-        if self.rank == 0 and ok:
-            os.close(fd.value)
+                if path[0] is not None:
+                    try:
+                        os.unlink(path[0])
+                    except OSError:
+                        pass
+            if fd.value >= 0:          # rank 0's exported descriptor: the peers hold their own copies
+                os.close(fd.value)
         with torch.cuda.device(self.device):
             ok = self._all_ok(ok, group) and lib.b200_nvls_add_device(buf) == 0
             ok = self._all_ok(ok, group)   # also the barrier between add_device and bind
