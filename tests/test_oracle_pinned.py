@@ -95,3 +95,19 @@ def test_gemv_stream_layout_oracle_against_scalar_loops():
                     assert got[idx] == w, (nt, kb, lane, j)
                     idx += 1
     assert idx == got.size
+
+
+def test_gptq_qweight_packing_matches_vllm_gptq_pack():
+    """Packing order of the GPTQ qweight tensor against vllm's own gptq_pack (the dependency the
+    reference delegates GPTQ to; fixture from oracle/gen_golden_gptq_pack.py).  The dequant
+    arithmetic stays unpinned (no CPU implementation in vllm)."""
+    import os
+
+    import torch
+
+    from oracle import int4 as O
+
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "gptq_pack_vllm.pt"))
+    assert gold["vllm_version"]
+    for c in gold["cases"]:
+        assert torch.equal(O.unpack_gptq_qweight(c["qweight"]).to(torch.int32), c["q"])
