@@ -16,5 +16,7 @@ Pinning status (details in DESIGN.md §3):
   scheduler index kernels : pinned — get_last_loc / compute_position by the reference's torch twins,
       alloc_extend / alloc_decode by the reference's own Triton kernels run in Triton's CPU
       interpreter (tests/golden/sched_index.pt, sched_alloc.pt).
-  GPTQ                    : parity unpinned (arithmetic lives in vllm 0.8.4, absent).
+  GPTQ                    : arithmetic lives in vllm 0.8.4 (absent, CUDA only): packing order pinned
+      by vllm's gptq_pack (tests/golden/gptq_pack_vllm.pt); dequant arithmetic checked on the GPU box
+      against the image's vllm wheel (tests/test_gptq_vs_vllm_gpu.py) - unpinned in the CPU suite.
 """

@@ -4,7 +4,7 @@ own `gptq_pack` (vllm/model_executor/layers/quantization/utils/quant_utils.py). 
 vllm 0.8.4 (python/sglang/srt/layers/quantization/gptq.py:17-31 imports it); the wheel present in
 this image is a later vllm (version recorded in the fixture) — the checkpoint format did not change.
 This pins the PACKING ORDER of oracle/int4.py::unpack_gptq_qweight only; the dequant arithmetic
-(zero + 1, exllama CUDA kernels) has no CPU implementation in vllm and stays "parity unpinned".
+(zero + 1, exllama CUDA kernels) has no CPU implementation in vllm; it is checked on the GPU box (tests/test_gptq_vs_vllm_gpu.py).
 TEST INFRASTRUCTURE ONLY."""
 import os
 import sys

@@ -100,7 +100,7 @@ def test_gemv_stream_layout_oracle_against_scalar_loops():
 def test_gptq_qweight_packing_matches_vllm_gptq_pack():
     """Packing order of the GPTQ qweight tensor against vllm's own gptq_pack (the dependency the
     reference delegates GPTQ to; fixture from oracle/gen_golden_gptq_pack.py).  The dequant
-    arithmetic stays unpinned (no CPU implementation in vllm)."""
+    arithmetic has no CPU implementation in vllm: it is checked on the GPU (test_gptq_vs_vllm_gpu.py)."""
     import os
 
     import torch
