@@ -30,6 +30,13 @@ enum b200_dtype {
   B200_F32 = 2,
   B200_FP8_E4M3 = 3
 };
+/* Flag OR'ed into the `dtype` argument of the FP8-KV-pool entry points (b200_kv_write_fp8,
+ * b200_rope_kv_write_fp8, b200_attn_decode_fp8kv[_fused], b200_kv_dequant_gather): the pool holds
+ * float8_e5m2 bytes (`--kv-cache-dtype fp8_e5m2`, model_runner.py:845-846) instead of e4m3.
+ * Writers then follow torch's `.to(torch.float8_e5m2)`: round-to-nearest-even, |x| >= 61440 -> Inf
+ * byte (sign | 0x7c), NaN -> sign | 0x7f.  The e5m2 decode kernel has no in-kernel tail: a ticket
+ * buffer passed to the _fused entry point is ignored (one merge / merge+quantise launch).        */
+#define B200_KV_FP8_E5M2 0x100
 
 /* ---- library ---------------------------------------------------------- */
 int b200_version(void);

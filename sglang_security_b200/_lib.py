@@ -15,6 +15,7 @@ _lib = None
 
 # dtype codes (enum b200_dtype)
 BF16, F16, F32, FP8_E4M3 = 0, 1, 2, 3
+KV_FP8_E5M2 = 0x100  # B200_KV_FP8_E5M2: flag on the dtype argument of the FP8-KV-pool entry points
 
 _SIGNATURES = {
     "b200_version": (c_int, []),
@@ -218,6 +219,19 @@ def dtype_code(torch_dtype) -> int:
     if torch_dtype not in table:
         raise B200Error(f"dtype {torch_dtype} is not supported by the B200 hot path")
     return table[torch_dtype]
+
+
+def is_fp8_kv(torch_dtype) -> bool:
+    import torch
+
+    return torch_dtype in (torch.float8_e4m3fn, torch.float8_e5m2)
+
+
+def kv_dtype_code(act_dtype, pool_dtype) -> int:
+    """dtype argument of an FP8-KV-pool entry point: activation dtype code | the e5m2 flag."""
+    import torch
+
+    return dtype_code(act_dtype) | (KV_FP8_E5M2 if pool_dtype == torch.float8_e5m2 else 0)
 
 
 def current_stream() -> int:

@@ -821,8 +821,34 @@ static int launch_decode_fp8kv(const DecodeParams& p, cudaStream_t st) {
                              : launch_decode_fp8kv_st<T, D, HI, 2>(p, st);
 }
 
+// e5m2 pool (`--kv-cache-dtype fp8_e5m2`): the same kernel with the byte -> f16 conversion swapped
+// (one PRMT instead of a cvt); 2-stage ring, no in-kernel tail.
+template <typename T, int D, bool HI>
+static int launch_decode_e5m2kv(const DecodeParams& p, cudaStream_t st) {
+  using C = Fp8KvCfg<D, kNT8, 2, kNW>;
+  auto kern = attn_decode_fp8kv_kernel<T, D, kNT8, 2, kNW, HI, false, true>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C::SMEM_BYTES));
+    attr_done = true;
+  }
+  dim3 grid(p.num_splits, p.Hkv * p.head_tiles, p.bs);
+  {
+    ScopedKernelTimer timer("attn_decode_fp8kv", st);
+    B200_CUDA_OK(launch_kernel(kern, grid, dim3(C::THREADS), C::SMEM_BYTES, st, 1,
+                               pdl_family(p.bs, kPdlAttn), p));
+  }
+  B200_CHECK_LAUNCH("attn_decode_fp8kv_kernel<e5m2>");
+  return 0;
+}
+
 template <typename T>
-static int dispatch_decode_fp8kv(const DecodeParams& p, int D, int G, cudaStream_t st) {
+static int dispatch_decode_fp8kv(const DecodeParams& p, int D, int G, bool e5m2, cudaStream_t st) {
+  if (e5m2 && D == 128)
+    return G > 8 ? launch_decode_e5m2kv<T, 128, true>(p, st) : launch_decode_e5m2kv<T, 128, false>(p, st);
+  if (e5m2 && D == 64)
+    return G > 8 ? launch_decode_e5m2kv<T, 64, true>(p, st) : launch_decode_e5m2kv<T, 64, false>(p, st);
   if (D == 128)
     return G > 8 ? launch_decode_fp8kv<T, 128, true>(p, st) : launch_decode_fp8kv<T, 128, false>(p, st);
   if (D == 64)
@@ -1027,6 +1053,15 @@ static int attn_decode_fp8kv_impl(const void* q, int64_t q_stride, const void* k
                                   void* stream, const b200::DecodeTail* tail) {
   using namespace b200;
   if (bs == 0) return 0;
+  const bool e5m2 = (dtype & B200_KV_FP8_E5M2) != 0;
+  dtype &= ~B200_KV_FP8_E5M2;
+  DecodeTail tail_e5m2;
+  if (e5m2 && tail && tail->tickets) {  // no in-kernel tail instance for e5m2: one merge launch
+    tail_e5m2 = *tail;
+    tail_e5m2.tickets = nullptr;
+    tail_e5m2.ticket_bytes = 0;
+    tail = &tail_e5m2;
+  }
   B200_REQUIRE(q && k_cache && v_cache && o && req_to_token && req_pool_indices && seq_lens,
                "b200_attn_decode_fp8kv: null pointer");
   B200_REQUIRE(bs > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0,
@@ -1072,8 +1107,8 @@ static int attn_decode_fp8kv_impl(const void* q, int64_t q_stride, const void* k
   p.part_lse = p.part_o ? p.part_o + static_cast<size_t>(bs) * Hq * num_splits * Dv : nullptr;
   if (int rc = apply_tail(p, tail, D, "b200_attn_decode_fp8kv_fused")) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, st)
-                                    : dispatch_decode_fp8kv<__half>(p, D, G, st);
+  const int rc = dtype == B200_BF16 ? dispatch_decode_fp8kv<__nv_bfloat16>(p, D, G, e5m2, st)
+                                    : dispatch_decode_fp8kv<__half>(p, D, G, e5m2, st);
   if (rc) return rc;
   if (tail && !tail->tickets && tail->q_out)
     return dtype == B200_BF16 ? launch_merge_quant<__nv_bfloat16>(p, Dv, decode_align_fp8kv(), st)

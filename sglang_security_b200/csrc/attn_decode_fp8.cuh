@@ -1,4 +1,5 @@
-// Paged split-KV decode attention over an FP8 (e4m3) KV pool — included by attn_decode.cu.
+// Paged split-KV decode attention over an FP8 (e4m3, or e5m2 with E5M2) KV pool — included by
+// attn_decode.cu.
 //
 // Path replaced: AttentionBackend.forward_decode with `--kv-cache-dtype fp8_e4m3`
 // (model_runner.py:845-858; pool stores e4m3 bytes, memory_pool.py:119-123,390-400; FlashInfer
@@ -45,15 +46,7 @@ __device__ __forceinline__ int fp8kv_swz(int row) {
   return RB == 128 ? (row & 7) : ((row >> 1) & 3);
 }
 
-// four e4m3 bytes -> two f16x2 registers (exact): lo = bytes 0,1; hi = bytes 2,3
-__device__ __forceinline__ void cvt_e4m3x4_f16x4(uint32_t x, uint32_t& lo, uint32_t& hi) {
-  asm("{\n\t.reg .b16 a, b;\n\t"
-      "mov.b32 {a, b}, %2;\n\t"
-      "cvt.rn.f16x2.e4m3x2 %0, a;\n\t"
-      "cvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
-      : "=r"(lo), "=r"(hi)
-      : "r"(x));
-}
+// fp8 bytes -> f16x2 registers: cvt_fp8x4_f16x4<E5M2> (common.cuh)
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;\n" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
@@ -78,7 +71,7 @@ __device__ __forceinline__ void q4_to_f16<__nv_bfloat16>(const __nv_bfloat16* q,
   hi = *reinterpret_cast<const uint32_t*>(&hb);
 }
 
-template <typename T, int D, int NT, int STAGES, int NW, bool HI, bool TAIL>
+template <typename T, int D, int NT, int STAGES, int NW, bool HI, bool TAIL, bool E5M2 = false>
 __global__ void __launch_bounds__(NW * 32, TAIL ? 4 : 0)
 attn_decode_fp8kv_kernel(const DecodeParams p) {
   using C = Fp8KvCfg<D, NT, STAGES, NW>;
@@ -215,7 +208,7 @@ attn_decode_fp8kv_kernel(const DecodeParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           uint32_t b0, b1;
-          cvt_e4m3x4_f16x4(kb[i], b0, b1);
+          cvt_fp8x4_f16x4<E5M2>(kb[i], b0, b1);
           mma16816<__half>(s[nt], qa[4 * jj + i], b0, b1);
         }
       }
@@ -298,8 +291,8 @@ attn_decode_fp8kv_kernel(const DecodeParams p) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {  // chunk j + h: vb[2h] = tokens 0-7, vb[2h+1] = tokens 8-15
           uint32_t l0, h0, l1, h1;
-          cvt_e4m3x4_f16x4(vb[2 * h], l0, h0);
-          cvt_e4m3x4_f16x4(vb[2 * h + 1], l1, h1);
+          cvt_fp8x4_f16x4<E5M2>(vb[2 * h], l0, h0);
+          cvt_fp8x4_f16x4<E5M2>(vb[2 * h + 1], l1, h1);
           const int t = 2 * (j + h);
           mma16816<__half>(o[t], pa[kt], prmt(l0, h0, 0x5410u), prmt(l1, h1, 0x5410u));
           mma16816<__half>(o[t + 1], pa[kt], prmt(l0, h0, 0x7632u), prmt(l1, h1, 0x7632u));

@@ -231,6 +231,39 @@ __device__ __forceinline__ uint32_t to_e4m3_torch(T x, float inv_is_div_scale, b
   if (!(fabsf(f) <= 464.f)) b = ((__float_as_uint(f) >> 24) & 0x80u) | 0x7fu;
   return b;
 }
-
+// Same for an e5m2 pool (`--kv-cache-dtype fp8_e5m2`, model_runner.py:845-858): torch's
+// `.to(torch.float8_e5m2)` is IEEE round-to-nearest-even WITH overflow to infinity (|x| >= 61440,
+// the midpoint between the last finite value 57344 and 2^16, becomes sign | 0x7c) and NaN -> sign | 0x7f;
+// the hardware conversion saturates to 57344 instead, so the two ranges are patched.
+template <typename T>
+__device__ __forceinline__ uint32_t to_e5m2_torch(T x, float inv_is_div_scale, bool has_scale) {
+  float f = to_float<T>(x);
+  if (has_scale) f = to_float<T>(from_float<T>(f / inv_is_div_scale));
+  uint16_t r;
+  asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(f));
+  uint32_t b = r & 0xffu;
+  const uint32_t sign = (__float_as_uint(f) >> 24) & 0x80u;
+  if (!(fabsf(f) < 61440.f)) b = sign | (f != f ? 0x7fu : 0x7cu);
+  return b;
+}
+template <typename T>
+__device__ __forceinline__ uint32_t to_fp8_torch(T x, float scale, bool has_scale, bool e5m2) {
+  return e5m2 ? to_e5m2_torch<T>(x, scale, has_scale) : to_e4m3_torch<T>(x, scale, has_scale);
+}
+// four fp8 bytes -> two f16x2 registers (exact): lo = bytes 0,1; hi = bytes 2,3
+template <bool E5M2>
+__device__ __forceinline__ void cvt_fp8x4_f16x4(uint32_t x, uint32_t& lo, uint32_t& hi) {
+  if (E5M2) {  // e5m2 is the high byte of an f16
+    asm("prmt.b32 %0, %1, 0, 0x1404;\n" : "=r"(lo) : "r"(x));
+    asm("prmt.b32 %0, %1, 0, 0x3424;\n" : "=r"(hi) : "r"(x));
+  } else {
+    asm("{\n\t.reg .b16 a, b;\n\t"
+        "mov.b32 {a, b}, %2;\n\t"
+        "cvt.rn.f16x2.e4m3x2 %0, a;\n\t"
+        "cvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+        : "=r"(lo), "=r"(hi)
+        : "r"(x));
+  }
+}
 
 }  // namespace b200

@@ -342,7 +342,8 @@ struct RopeParams {
   int64_t cache_row_stride;
   const int64_t* loc;
   int Hq, Hkv, D;
-  // e4m3 pool (b200_rope_kv_write_fp8): rows are bytes, values quantised as b200_kv_write_fp8 does
+  // FP8 pool (b200_rope_kv_write_fp8): rows are bytes, values quantised as b200_kv_write_fp8 does;
+  // 0 = 16-bit pool, 1 = e4m3, 2 = e5m2
   int cache_fp8;
   float k_scale, v_scale;
   int has_scale;
@@ -356,8 +357,8 @@ __device__ __forceinline__ void st_cache8(const RopeParams& p, uint8_t* row, int
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      lo |= to_e4m3_torch<T>(from_float<T>(f[j]), scale, p.has_scale != 0) << (8 * j);
-      hi |= to_e4m3_torch<T>(from_float<T>(f[4 + j]), scale, p.has_scale != 0) << (8 * j);
+      lo |= to_fp8_torch<T>(from_float<T>(f[j]), scale, p.has_scale != 0, p.cache_fp8 == 2) << (8 * j);
+      hi |= to_fp8_torch<T>(from_float<T>(f[4 + j]), scale, p.has_scale != 0, p.cache_fp8 == 2) << (8 * j);
     }
     *reinterpret_cast<uint2*>(row + off) = make_uint2(lo, hi);
   } else {
@@ -653,12 +654,14 @@ int b200_rope_kv_write_fp8(const int64_t* positions, void* q, int64_t q_stride, 
                            int64_t cache_row_stride, const int64_t* loc, float k_scale,
                            float v_scale, int has_scale, int T, int Hq, int Hkv, int D, int dtype,
                            void* stream) {
-  B200_REQUIRE(k_cache && v_cache, "b200_rope_kv_write_fp8: the e4m3 pool rows are required");
+  B200_REQUIRE(k_cache && v_cache, "b200_rope_kv_write_fp8: the FP8 pool rows are required");
+  const int fmt = (dtype & B200_KV_FP8_E5M2) ? 2 : 1;
+  dtype &= ~B200_KV_FP8_E5M2;
   B200_REQUIRE(!has_scale || (k_scale > 0.f && v_scale > 0.f),
                "b200_rope_kv_write_fp8: scales must be positive");
   return rope_kv_write_impl(positions, q, q_stride, k, k_stride, v, v_stride, cos_sin_cache,
                             cache_dtype, rotary_dim, is_neox, native_rounding, k_cache, v_cache,
-                            cache_row_stride, loc, 1, k_scale, v_scale, has_scale, T, Hq, Hkv, D,
+                            cache_row_stride, loc, fmt, k_scale, v_scale, has_scale, T, Hq, Hkv, D,
                             dtype, stream);
 }
 

@@ -41,7 +41,7 @@ __global__ void kv_write_fp8_kernel(const T* __restrict__ k, const T* __restrict
                                     int64_t k_stride, int64_t v_stride,
                                     uint8_t* __restrict__ k_cache, uint8_t* __restrict__ v_cache,
                                     const int64_t* __restrict__ loc, int num_tokens, int row_elems,
-                                    float k_scale, float v_scale, int has_scale) {
+                                    float k_scale, float v_scale, int has_scale, int e5m2) {
   griddep_wait();
   griddep_launch_dependents();
   const bool is_v = blockIdx.y != 0;
@@ -61,8 +61,8 @@ __global__ void kv_write_fp8_kernel(const T* __restrict__ k, const T* __restrict
     uint32_t lo = 0, hi = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      lo |= to_e4m3_torch<T>(e[j], scale, has_scale != 0) << (8 * j);
-      hi |= to_e4m3_torch<T>(e[4 + j], scale, has_scale != 0) << (8 * j);
+      lo |= to_fp8_torch<T>(e[j], scale, has_scale != 0, e5m2 != 0) << (8 * j);
+      hi |= to_fp8_torch<T>(e[4 + j], scale, has_scale != 0, e5m2 != 0) << (8 * j);
     }
     *reinterpret_cast<uint2*>(dst + slot * row_elems + c * 8) = make_uint2(lo, hi);
   }
@@ -79,7 +79,7 @@ __global__ void kv_dequant_gather_kernel(const uint8_t* __restrict__ k8, const u
                                          const int64_t* __restrict__ seq_lens,
                                          const int32_t* __restrict__ kv_indptr, T* __restrict__ k_out,
                                          T* __restrict__ v_out, int32_t* __restrict__ dense_rtt,
-                                         int64_t dense_rtt_stride) {
+                                         int64_t dense_rtt_stride, int e5m2) {
   griddep_wait();
   griddep_launch_dependents();
   const int b = blockIdx.y;
@@ -104,10 +104,8 @@ __global__ void kv_dequant_gather_kernel(const uint8_t* __restrict__ k8, const u
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         uint32_t lo, hi;
-        asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\t"
-            "cvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
-            : "=r"(lo), "=r"(hi)
-            : "r"(w[h]));
+        if (e5m2) cvt_fp8x4_f16x4<true>(w[h], lo, hi);
+        else cvt_fp8x4_f16x4<false>(w[h], lo, hi);
         if (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
           const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&lo));
           const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&hi));
@@ -198,6 +196,8 @@ int b200_kv_write_fp8(const void* k, const void* v, int64_t k_token_stride,
   B200_REQUIRE(k && v && k_cache && v_cache && loc, "b200_kv_write_fp8: null pointer");
   B200_REQUIRE(num_tokens > 0 && row_elems > 0 && row_elems % 8 == 0,
                "b200_kv_write_fp8: bad sizes (tokens=%d, row_elems=%d)", num_tokens, row_elems);
+  const int e5m2 = (dtype & B200_KV_FP8_E5M2) ? 1 : 0;
+  dtype &= ~B200_KV_FP8_E5M2;
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, "b200_kv_write_fp8: source dtype %d", dtype);
   B200_REQUIRE(aligned16(k) && aligned16(v) && k_token_stride % 8 == 0 && v_token_stride % 8 == 0 &&
                    (reinterpret_cast<uintptr_t>(k_cache) & 7u) == 0 &&
@@ -218,13 +218,13 @@ int b200_kv_write_fp8(const void* k, const void* v, int64_t k_token_stride,
                          pdl_family(num_tokens, kPdlOther), static_cast<const __nv_bfloat16*>(k),
                          static_cast<const __nv_bfloat16*>(v), k_token_stride, v_token_stride,
                          static_cast<uint8_t*>(k_cache), static_cast<uint8_t*>(v_cache), loc,
-                         num_tokens, row_elems, k_scale, v_scale, has_scale);
+                         num_tokens, row_elems, k_scale, v_scale, has_scale, e5m2);
   else
     lerr = launch_kernel(kv_write_fp8_kernel<__half>, grid, dim3(256), 0, st, 1,
                          pdl_family(num_tokens, kPdlOther), static_cast<const __half*>(k),
                          static_cast<const __half*>(v), k_token_stride, v_token_stride,
                          static_cast<uint8_t*>(k_cache), static_cast<uint8_t*>(v_cache), loc,
-                         num_tokens, row_elems, k_scale, v_scale, has_scale);
+                         num_tokens, row_elems, k_scale, v_scale, has_scale, e5m2);
   B200_CUDA_OK(lerr);
   B200_CHECK_LAUNCH("b200_kv_write_fp8");
   return 0;
@@ -243,6 +243,8 @@ int b200_kv_dequant_gather(const void* k_cache, const void* v_cache, int row_ele
                "b200_kv_dequant_gather: null pointer");
   B200_REQUIRE(row_elems > 0 && row_elems % 8 == 0 && bs > 0 && bs <= 65535,
                "b200_kv_dequant_gather: bad sizes (row_elems=%d bs=%d)", row_elems, bs);
+  const int e5m2 = (dtype & B200_KV_FP8_E5M2) ? 1 : 0;
+  dtype &= ~B200_KV_FP8_E5M2;
   B200_REQUIRE(dtype == B200_BF16 || dtype == B200_F16, "b200_kv_dequant_gather: dtype %d", dtype);
   B200_REQUIRE((reinterpret_cast<uintptr_t>(k_cache) & 7u) == 0 &&
                    (reinterpret_cast<uintptr_t>(v_cache) & 7u) == 0 && aligned16(k_out) &&
@@ -263,13 +265,13 @@ int b200_kv_dequant_gather(const void* k_cache, const void* v_cache, int row_ele
                          static_cast<const uint8_t*>(v_cache), row_elems, req_to_token,
                          req_to_token_stride, req_pool_indices, seq_lens, kv_indptr,
                          static_cast<__nv_bfloat16*>(k_out), static_cast<__nv_bfloat16*>(v_out),
-                         dense_rtt, dense_rtt_stride);
+                         dense_rtt, dense_rtt_stride, e5m2);
   else
     lerr = launch_kernel(kv_dequant_gather_kernel<__half>, grid, dim3(256), 0, st, 1, kPdlOther & 0,
                          static_cast<const uint8_t*>(k_cache), static_cast<const uint8_t*>(v_cache),
                          row_elems, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
                          kv_indptr, static_cast<__half*>(k_out), static_cast<__half*>(v_out),
-                         dense_rtt, dense_rtt_stride);
+                         dense_rtt, dense_rtt_stride, e5m2);
   B200_CUDA_OK(lerr);
   B200_CHECK_LAUNCH("b200_kv_dequant_gather");
   return 0;

@@ -259,11 +259,11 @@ class B200AttnBackend(AttentionBackend):
         # kernels read int64, so convert once per forward and hold the copies in the metadata
         req_pool_indices = md.as_dtype(forward_batch.req_pool_indices, torch.int64)
         seq_lens = md.as_dtype(forward_batch.seq_lens, torch.int64)
-        fp8kv = k_cache.dtype == torch.float8_e4m3fn
+        fp8kv = _lib.is_fp8_kv(k_cache.dtype)
         if not fp8kv and k_cache.dtype != q.dtype:
             raise _lib.B200Error(
                 f"B200AttnBackend.forward_decode: KV cache dtype {k_cache.dtype} != q dtype "
-                f"{q.dtype} (supported pools: the activation dtype or float8_e4m3fn)")
+                f"{q.dtype} (supported pools: the activation dtype, float8_e4m3fn or float8_e5m2)")
         common = (q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
                   k_cache.stride(0), o.data_ptr(), o.stride(0), req_to_token.data_ptr(),
                   req_to_token.stride(0), req_pool_indices.data_ptr(), seq_lens.data_ptr(), bs, hq,
@@ -271,8 +271,8 @@ class B200AttnBackend(AttentionBackend):
         if fp8kv:
             ks, vs = self._kv_scales(layer)
             common = common + (1.0 if ks is None else ks, 1.0 if vs is None else vs)
-        common = common + (_lib.dtype_code(q.dtype), _lib.ptr(ws), 0 if ws is None else ws.numel(),
-                           md.num_splits)
+        common = common + (_lib.kv_dtype_code(q.dtype, k_cache.dtype), _lib.ptr(ws),
+                           0 if ws is None else ws.numel(), md.num_splits)
         # the tail only pays when it replaces a launch: the merge (splits > 1) or the quantiser
         fused = self.fused_tail and (md.num_splits > 1 or fp8_out) and (hq * dv) % 8 == 0
         if fused:
@@ -335,7 +335,7 @@ class B200AttnBackend(AttentionBackend):
         prefix_lens = md.as_dtype(forward_batch.extend_prefix_lens, torch.int32)
         extend_lens = md.as_dtype(forward_batch.extend_seq_lens, torch.int32)
         scaling, out_scale = float(layer.scaling), 1.0
-        if k_cache.dtype == torch.float8_e4m3fn:
+        if _lib.is_fp8_kv(k_cache.dtype):
             # FP8 pool: the tcgen05 kernel wants 16-bit operands, so the requests' rows are first
             # copied (exactly) into a dense 16-bit scratch; scales ride on the softmax scale / output
             k_cache, v_cache, req_to_token, req_pool_indices = self._dequant_for_extend(
@@ -347,7 +347,7 @@ class B200AttnBackend(AttentionBackend):
         elif k_cache.dtype != q.dtype:
             raise _lib.B200Error(
                 f"B200AttnBackend.forward_extend: KV cache dtype {k_cache.dtype} != q dtype "
-                f"{q.dtype} (supported pools: the activation dtype or float8_e4m3fn)")
+                f"{q.dtype} (supported pools: the activation dtype, float8_e4m3fn or float8_e5m2)")
         rc = self.lib.b200_attn_extend_scaled(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
             o.data_ptr(), o.stride(0), req_to_token.data_ptr(), req_to_token.stride(0),
@@ -360,7 +360,7 @@ class B200AttnBackend(AttentionBackend):
 
     def _dequant_for_extend(self, forward_batch, k_cache, v_cache, req_to_token, req_pool_indices,
                             seq_lens, row_elems, dtype):
-        """-> (k16, v16, dense_req_to_token, dense_req_pool_indices) for an e4m3 pool."""
+        """-> (k16, v16, dense_req_to_token, dense_req_pool_indices) for an e4m3 / e5m2 pool."""
         bs = seq_lens.numel()
         cpu = getattr(forward_batch, "seq_lens_cpu", None)
         if cpu is not None:
@@ -377,7 +377,7 @@ class B200AttnBackend(AttentionBackend):
             k_cache.data_ptr(), v_cache.data_ptr(), row_elems, req_to_token.data_ptr(),
             req_to_token.stride(0), req_pool_indices.data_ptr(), seq_lens.data_ptr(),
             indptr.data_ptr(), k16.data_ptr(), v16.data_ptr(), dense_rtt.data_ptr(), stride, bs,
-            max_len, _lib.dtype_code(dtype), _lib.current_stream())
+            max_len, _lib.kv_dtype_code(dtype, k_cache.dtype), _lib.current_stream())
         _lib.check(rc, "b200_kv_dequant_gather")
         return k16, v16, dense_rtt, torch.arange(bs, dtype=torch.int64, device=seq_lens.device)
 

@@ -42,7 +42,8 @@ class RotaryEmbedding(nn.Module):
         freqs = torch.einsum("i,j -> ij", t, inv_freq)
         return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
 
-    def _launch(self, positions, query, key, value, k_cache, v_cache, loc, fp8_scales=None):
+    def _launch(self, positions, query, key, value, k_cache, v_cache, loc, fp8_scales=None,
+                pool_dtype=None):
         if not query.is_cuda:
             raise _lib.B200Error("RotaryEmbedding: tensors must live on a CUDA device (no CPU path)")
         t = positions.numel()
@@ -60,7 +61,7 @@ class RotaryEmbedding(nn.Module):
             cache = cache.to(query.device)
             self.cos_sin_cache = cache
         v2 = value.view(t, -1) if value is not None else None
-        if fp8_scales is not None:  # e4m3 pool: rotate + quantising scatter in one launch
+        if fp8_scales is not None:  # FP8 pool: rotate + quantising scatter in one launch
             ks, vs = fp8_scales
             rc = _lib.load().b200_rope_kv_write_fp8(
                 pos.data_ptr(), q2.data_ptr(), q2.stride(0), k2.data_ptr(), k2.stride(0),
@@ -68,8 +69,8 @@ class RotaryEmbedding(nn.Module):
                 self.rotary_dim, 1 if self.is_neox_style else 0, 1 if self.native_rounding else 0,
                 k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0), loc.data_ptr(),
                 float(ks) if ks is not None else 1.0, float(vs) if vs is not None else 1.0,
-                0 if ks is None else 1, t, hq, hkv, self.head_size, _lib.dtype_code(query.dtype),
-                _lib.current_stream())
+                0 if ks is None else 1, t, hq, hkv, self.head_size,
+                _lib.kv_dtype_code(query.dtype, pool_dtype), _lib.current_stream())
             _lib.check(rc, "b200_rope_kv_write_fp8")
             return
         rc = _lib.load().b200_rope_kv_write(
@@ -98,7 +99,7 @@ class RotaryEmbedding(nn.Module):
         loc = forward_batch.out_cache_loc
         if loc.dtype != torch.int64:
             loc = loc.to(torch.int64)
-        if k_cache.dtype == torch.float8_e4m3fn:
+        if _lib.is_fp8_kv(k_cache.dtype):
             # FP8 pool: the quantising scatter of b200_kv_write_fp8 inside the RoPE kernel; scales as
             # in FlashInfer's set_kv_buffer call (flashinfer_backend.py:427), given together or not at all
             ks = getattr(layer, "k_scale_float", None)
@@ -109,7 +110,8 @@ class RotaryEmbedding(nn.Module):
                 raise _lib.B200Error("forward_with_kv_write: FP8 KV pool rows must be contiguous")
             self._launch(positions, query, key, value,
                          k_cache.view(k_cache.shape[0], -1).view(torch.uint8),
-                         v_cache.view(v_cache.shape[0], -1).view(torch.uint8), loc, (ks, vs))
+                         v_cache.view(v_cache.shape[0], -1).view(torch.uint8), loc, (ks, vs),
+                         k_cache.dtype)
             return query, key
         if k_cache.dtype != key.dtype:
             raise _lib.B200Error("forward_with_kv_write: KV pool dtype differs from the activations")

@@ -129,13 +129,13 @@ class MHATokenToKVPool:
         if cache_k.dtype != self.dtype:
             # FP8 pool: divide by the scale, cast and scatter in ONE kernel, bit-exact with the
             # reference's `div_` -> `.to(fp8)` -> index_put (memory_pool.py:390-412)
-            if self.dtype != torch.float8_e4m3fn:
+            if not _lib.is_fp8_kv(self.dtype):
                 raise _lib.B200Error(f"KV cache dtype {self.dtype} is not supported "
-                                     "(bf16/f16 or float8_e4m3fn)")
+                                     "(bf16/f16, float8_e4m3fn or float8_e5m2)")
             if (k_scale is None) != (v_scale is None):
                 raise _lib.B200Error("set_kv_buffer: k_scale and v_scale must be given together")
             kv_write_fp8(cache_k, cache_v, self.k_buffer[idx], self.v_buffer[idx], loc,
-                         k_scale, v_scale)
+                         k_scale, v_scale, self.dtype)
             return
         kv_write(cache_k, cache_v, self.k_buffer[idx], self.v_buffer[idx], loc)
 
@@ -145,9 +145,10 @@ def _scale_value(s) -> float:
 
 
 def kv_write_fp8(k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
-                 loc: torch.Tensor, k_scale=None, v_scale=None) -> None:
-    """Quantising scatter into an e4m3 pool stored as bytes (b200_kv_write_fp8).  Scales are host
-    floats (RadixAttention.k_scale_float / v_scale_float) so no device sync is needed."""
+                 loc: torch.Tensor, k_scale=None, v_scale=None,
+                 pool_dtype=torch.float8_e4m3fn) -> None:
+    """Quantising scatter into an e4m3 (or e5m2) pool stored as bytes (b200_kv_write_fp8).  Scales
+    are host floats (RadixAttention.k_scale_float / v_scale_float) so no device sync is needed."""
     if not k.is_cuda:
         raise _lib.B200Error("kv_write_fp8: tensors must live on a CUDA device (no CPU path)")
     num_tokens = loc.numel()
@@ -168,7 +169,7 @@ def kv_write_fp8(k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cach
     rc = _lib.load().b200_kv_write_fp8(
         k.data_ptr(), v.data_ptr(), k.stride(0), v.stride(0), k_cache.data_ptr(),
         v_cache.data_ptr(), loc.data_ptr(), num_tokens, row, _scale_value(k_scale),
-        _scale_value(v_scale), 0 if k_scale is None else 1, _lib.dtype_code(k.dtype),
+        _scale_value(v_scale), 0 if k_scale is None else 1, _lib.kv_dtype_code(k.dtype, pool_dtype),
         _lib.current_stream())
     _lib.check(rc, "b200_kv_write_fp8")
 
