@@ -46,8 +46,15 @@ def test_kv_write_e5m2_bit_exact(dtype, scales):
     pool.set_kv_buffer(SimpleNamespace(layer_id=0), loc.cuda(), kd, vd, ks, vs)
     torch.cuda.synchronize()
     got_k, got_v = pool.k_buffer[0].cpu(), pool.v_buffer[0].cpu()
-    bad = (got_k != ref.k_buffer[0]).nonzero()
-    assert bad.numel() == 0, (bad[:8].tolist(), got_k[tuple(bad[0])].item(), ref.k_buffer[0][tuple(bad[0])].item())
+    # the sign of a NaN that went through div_ is the platform's (the GPU returns the canonical
+    # positive NaN, the CPU keeps the operand's): NaN codes are compared without their sign bit here
+    # and exactly against torch's own CUDA cast below
+    want_k = ref.k_buffer[0].clone()
+    nan = (want_k & 0x7f) == 0x7f
+    assert torch.equal(nan, (got_k & 0x7f) == 0x7f)
+    want_k[nan] = got_k[nan]
+    bad = (got_k != want_k).nonzero()
+    assert bad.numel() == 0, (bad[:8].tolist(), got_k[tuple(bad[0])].item(), want_k[tuple(bad[0])].item())
     assert torch.equal(got_v, ref.v_buffer[0])
     # the same rows through torch's own CUDA cast (the reference's device path)
     dev = (kd.clone().div_(ks) if ks is not None else kd).to(E5M2).view(torch.uint8).cpu()
