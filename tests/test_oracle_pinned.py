@@ -111,3 +111,23 @@ def test_gptq_qweight_packing_matches_vllm_gptq_pack():
     assert gold["vllm_version"]
     for c in gold["cases"]:
         assert torch.equal(O.unpack_gptq_qweight(c["qweight"]).to(torch.int32), c["q"])
+
+
+def test_fp8_pool_write_oracle_equals_reference_method():
+    """oracle/pools.py set_kv_buffer on e4m3 and e5m2 pools against the bytes the reference's own
+    MHATokenToKVPool.set_kv_buffer wrote (memory_pool.py:378-412, extracted and run by
+    oracle/gen_golden_kv_write.py): div_ by the scales, cast, byte view, index_put."""
+    from types import SimpleNamespace
+
+    from oracle.pools import OracleMHATokenToKVPool
+
+    gold = _load("kv_write_fp8")
+    assert len(gold["cases"]) == 12
+    for c in gold["cases"]:
+        pool_dtype = getattr(torch, c["pool_dtype"].split(".")[-1])
+        pool = OracleMHATokenToKVPool(100, 1, pool_dtype, c["k"].shape[1], c["k"].shape[2], 1)
+        ks, vs = c["scales"] if c["scales"] else (None, None)
+        pool.set_kv_buffer(SimpleNamespace(layer_id=0), c["loc"], c["k"].clone(), c["v"].clone(), ks, vs)
+        assert torch.equal(pool.k_buffer[0][c["loc"]], c["k_rows"]), (c["pool_dtype"], c["dtype"], c["scales"])
+        assert torch.equal(pool.v_buffer[0][c["loc"]], c["v_rows"])
+        assert pool.get_key_buffer(0).dtype == pool_dtype

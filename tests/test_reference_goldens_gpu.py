@@ -69,3 +69,26 @@ def test_fp8_block_mm_kernel_vs_reference_function():
                                       c["b_s"].cuda(), ref.dtype)
         rel = (out.cpu().float() - ref.float()).abs().mean() / ref.float().abs().mean()
         assert rel.item() < 1e-3, rel.item()
+
+
+def test_fp8_pool_write_kernel_equals_reference_method():
+    """b200_kv_write_fp8 (e4m3 and e5m2 pools) against the bytes the reference's own
+    MHATokenToKVPool.set_kv_buffer wrote on CPU (tests/golden/kv_write_fp8.pt,
+    oracle/gen_golden_kv_write.py); untouched rows stay zero."""
+    from types import SimpleNamespace
+
+    from sglang_security_b200.mem_cache.memory_pool import MHATokenToKVPool
+
+    for c in _load("kv_write_fp8")["cases"]:
+        pool_dtype = getattr(torch, c["pool_dtype"].split(".")[-1])
+        t, hkv, d = c["k"].shape
+        pool = MHATokenToKVPool(100, 1, pool_dtype, hkv, d, 1, "cuda")
+        ks, vs = c["scales"] if c["scales"] else (None, None)
+        pool.set_kv_buffer(SimpleNamespace(layer_id=0), c["loc"].cuda(), c["k"].cuda(), c["v"].cuda(), ks, vs)
+        torch.cuda.synchronize()
+        kb, vb = pool.k_buffer[0].cpu(), pool.v_buffer[0].cpu()
+        assert torch.equal(kb[c["loc"]], c["k_rows"]), (c["pool_dtype"], c["dtype"], c["scales"])
+        assert torch.equal(vb[c["loc"]], c["v_rows"])
+        untouched = torch.ones(kb.shape[0], dtype=torch.bool)
+        untouched[c["loc"]] = False
+        assert not kb[untouched].any() and not vb[untouched].any()
