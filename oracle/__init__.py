@@ -10,7 +10,8 @@ Pinning status (details in DESIGN.md §3):
       torch_native_backend.py run in the authoring container (tests/golden/attn_*.pt, generated
       by oracle/gen_golden.py) and against the reference sgl-kernel CPU kernels (oracle/_ref).
   pools / kv-indices      : pinned by the same fixtures (bit-exact) and the reference test's
-      python-loop definition (test/srt/test_create_kvindices.py:40-49).
+      python-loop definition (test/srt/test_create_kvindices.py:40-49); FP8 (e4m3 / e5m2) pool
+      writes by the reference's own set_kv_buffer run on CPU (tests/golden/kv_write_fp8.pt).
   FP8 quant / GEMM, AWQ   : restatements of the torch references inside the reference's tests
       (file:line in each function); pinned by fixtures generated from those test files.
   scheduler index kernels : pinned — get_last_loc / compute_position by the reference's torch twins,
