@@ -78,3 +78,42 @@ def test_restatement_matches_reference_cpu_kernel(name):
     assert torch.equal(kc, k_ref) and torch.equal(vc, v_ref)      # its fused KV write
     st = harness.error_stats(o.reshape(o.shape[0], -1), o_ref)
     assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, st
+
+
+def _triton_golden():
+    return torch.load(os.path.join(GOLDEN, "triton_attn.pt"), weights_only=False)["cases"]
+
+
+def triton_case(g):
+    kw = dict(g["kwargs"])
+    kw.pop("logit_cap", None)
+    kw["dtype"] = getattr(torch, kw["dtype"].split(".")[-1])
+    case = scenarios.make_attention_case(**kw)
+    assert scenarios.digest(case) == g["input_digest"], "synthetic inputs drifted from the fixture"
+    return case
+
+
+TRITON_CASES = ["decode_llama_g4_d128", "decode_qwen_g7_d64", "decode_g8_d128", "decode_mha_f16",
+                "decode_shared_prefix", "extend_llama_g4_d128", "extend_qwen_g7_d64",
+                "extend_shared_prefix", "decode_qwen_g7_d64_cap", "extend_llama_g4_d128_cap"]
+
+
+@pytest.mark.parametrize("name", TRITON_CASES)
+def test_restatement_matches_reference_triton_kernels(name):
+    """Third reference implementation: the reference's own Triton decode (split-KV stage 1 + 2,
+    MHA and grouped kernels) and extend kernels, run through Triton's CPU interpreter in float16
+    (oracle/gen_golden_triton_attn.py).  Both sides do fp32 math with one f16 output rounding, so
+    the bound is a few f16 ulps, far inside the 3e-2 / 1e-2 parity tolerance."""
+    g = _triton_golden()[name]
+    case = triton_case(g)
+    o, _, _ = harness.oracle_run(case, logit_cap=g["logit_cap"])
+    st = harness.error_stats(o, g["o"])
+    assert st["max_abs"] <= 4e-3 and st["rel_l2"] <= 2e-3, st
+
+
+def test_triton_golden_covers_every_case():
+    g = _triton_golden()
+    assert sorted(g) == sorted(TRITON_CASES)
+    # logit capping changed the result of the capped cases (the fixture really exercises it)
+    assert not torch.equal(g["decode_qwen_g7_d64_cap"]["o"], g["decode_qwen_g7_d64"]["o"])
+    assert not torch.equal(g["extend_llama_g4_d128_cap"]["o"], g["extend_llama_g4_d128"]["o"])

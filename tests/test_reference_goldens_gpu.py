@@ -92,3 +92,24 @@ def test_fp8_pool_write_kernel_equals_reference_method():
         untouched = torch.ones(kb.shape[0], dtype=torch.bool)
         untouched[c["loc"]] = False
         assert not kb[untouched].any() and not vb[untouched].any()
+
+
+@pytest.mark.parametrize("splits", [0, 3])
+def test_attention_kernels_vs_reference_triton_kernels(splits):
+    """B200AttnBackend decode / extend against the outputs of the reference's own Triton kernels
+    (tests/golden/triton_attn.pt: decode stage 1 + 2 and extend, run through Triton's CPU
+    interpreter by oracle/gen_golden_triton_attn.py), float16, incl. logit capping."""
+    import harness
+    from oracle import scenarios
+
+    gold = _load("triton_attn")["cases"]
+    assert len(gold) == 10
+    for name, g in gold.items():
+        kw = dict(g["kwargs"])
+        kw.pop("logit_cap", None)
+        kw["dtype"] = getattr(torch, kw["dtype"].split(".")[-1])
+        case = scenarios.make_attention_case(**kw)
+        assert scenarios.digest(case) == g["input_digest"]
+        o, _, _ = harness.b200_run(case, logit_cap=g["logit_cap"], num_kv_splits=splits)
+        st = harness.error_stats(o, g["o"])
+        assert st["max_abs"] <= 3e-2 and st["rel_l2"] <= 1e-2, (name, st)
