@@ -120,6 +120,25 @@ int b200_attn_decode(const void* q, int64_t q_stride, const void* k_cache, const
                      int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
                      void* workspace, size_t workspace_bytes, int num_splits, void* stream);
 
+/* b200_attn_decode for callers that cannot allocate device memory (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same operands, math and kernels as b200_attn_decode, minus the workspace:
+ * the split-KV partials go to a scratch array built into the library (one per GPU that loads it,
+ * held until exit).  The call allocates nothing (no cudaMalloc / cudaFree / allocating library call).
+ * Limit: b200_attn_decode_workspace_bytes(bs, Hq, Dv, num_splits) must not exceed
+ * B200_ATTN_DECODE_NOALLOC_SCRATCH_BYTES (8 MiB: e.g. 64 requests x 32 heads x 7 splits at Dv 128);
+ * larger requests are rejected with an error (status 1, b200_last_error()), nothing is launched.
+ * The device that owns `stream` must be current.  Every call on a device shares the scratch and
+ * finds the previous call's contents in it (none of it has to be zero); calls that overlap on the
+ * GPU (different streams, concurrent graph launches) race on it - serialise them on one stream.  */
+#define B200_ATTN_DECODE_NOALLOC_SCRATCH_BYTES (8u << 20)
+int b200_attn_decode_noalloc(const void* q, int64_t q_stride, const void* k_cache,
+                             const void* v_cache, int64_t kv_row_stride, void* o, int64_t o_stride,
+                             const int32_t* req_to_token, int64_t req_to_token_stride,
+                             const int64_t* req_pool_indices, const int64_t* seq_lens, int bs,
+                             int Hq, int Hkv, int D, int Dv, float scale, float logit_cap, int dtype,
+                             int num_splits, void* stream);
+
 /* Same contract over an FP8 (e4m3) KV pool (k_cache/v_cache rows of D bytes, kv_row_stride in
  * bytes): o = v_scale * softmax(scale * k_scale * q.K8^T) @ V8 — FlashInfer-backend semantics
  * (flashinfer_backend.py:499-509); pass 1.0 for the Triton backend's scale-free reading

@@ -58,6 +58,11 @@ _SIGNATURES = {
                                  c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
                                  c_int, c_int, c_int, c_float, c_float, c_int, c_void_p, c_size_t,
                                  c_int, c_void_p]),
+    # split-KV scratch built into the library (8 MiB, B200_ATTN_DECODE_NOALLOC_SCRATCH_BYTES): allocates nothing
+    "b200_attn_decode_noalloc": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                         c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
+                                         c_int, c_int, c_int, c_float, c_float, c_int, c_int,
+                                         c_void_p]),
     "b200_attn_decode_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
                                        c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_int, c_int, c_float, c_float, c_int, c_void_p,
