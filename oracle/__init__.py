@@ -8,7 +8,9 @@ product path.  Nothing under `sglang_security_b200/` imports it.
 Pinning status (details in DESIGN.md §3):
   attention decode/extend : pinned — checked against outputs of the reference's own
       torch_native_backend.py run in the authoring container (tests/golden/attn_*.pt, generated
-      by oracle/gen_golden.py) and against the reference sgl-kernel CPU kernels (oracle/_ref).
+      by oracle/gen_golden.py), against the reference sgl-kernel CPU kernels (oracle/_ref) and
+      against the reference's own Triton decode / extend kernels run in Triton's CPU interpreter
+      (tests/golden/triton_attn.pt, oracle/gen_golden_triton_attn.py).
   pools / kv-indices      : pinned by the same fixtures (bit-exact) and the reference test's
       python-loop definition (test/srt/test_create_kvindices.py:40-49); FP8 (e4m3 / e5m2) pool
       writes by the reference's own set_kv_buffer run on CPU (tests/golden/kv_write_fp8.pt).
