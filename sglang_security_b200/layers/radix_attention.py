@@ -16,7 +16,8 @@ class RadixAttention(nn.Module):
     def __init__(self, num_heads: int, head_dim: int, scaling: float, num_kv_heads: int,
                  layer_id: int, logit_cap: float = 0.0, v_head_dim: int = -1,
                  sliding_window_size: int = -1, is_cross_attention: bool = False,
-                 attn_type: AttentionType = AttentionType.DECODER):
+                 attn_type: AttentionType = AttentionType.DECODER, quant_config=None,
+                 prefix: str = ""):
         super().__init__()
         self.tp_q_head_num = num_heads
         self.tp_k_head_num = num_kv_heads
@@ -34,6 +35,13 @@ class RadixAttention(nn.Module):
         self.v_scale = None
         self.k_scale_float = None   # host copies (radix_attention.py:74-75): no .item() per step
         self.v_scale_float = None
+        # a KV-cache quant method (layers/quantization/kv_cache.py) turns k_scale / v_scale into
+        # loadable parameters (radix_attention.py:76-80)
+        self.quant_method = None
+        if quant_config is not None:
+            self.quant_method = quant_config.get_quant_method(self, prefix=prefix)
+        if self.quant_method is not None:
+            self.quant_method.create_weights(self)
 
     def forward(self, q, k, v, forward_batch, save_kv_cache: bool = True, **kwargs):
         if k is not None:

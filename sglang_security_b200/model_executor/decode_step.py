@@ -157,6 +157,15 @@ class B200DecodeStep:
         self.final_norm = RMSNorm(g.hidden, g.rms_eps).to(device)
         self.final_norm.weight.data = self.final_norm.weight.data.to(torch.bfloat16)
 
+    # ------------------------------------------------------------------ FP8 KV-cache scales
+    def load_kv_cache_scales(self, quantization_param_path: str, model_type: Optional[str] = None) -> int:
+        """`--quantization-param-path` (model_runner.py:560-569 -> models/llama.py:359-378): per-layer
+        k/v scaling factors of an FP8 KV pool from the reference's JSON format.  -> layers set."""
+        from ..model_loader.weight_utils import load_kv_cache_scales
+
+        return load_kv_cache_scales([L.attn for L in self.layers], quantization_param_path,
+                                    self.tp_rank, self.tp_size, model_type)
+
     # ------------------------------------------------------------------ byte accounting
     def linear_weight_bytes(self) -> int:
         n = 0
