@@ -37,11 +37,10 @@ class RadixAttention(nn.Module):
         self.v_scale_float = None
         # a KV-cache quant method (layers/quantization/kv_cache.py) turns k_scale / v_scale into
         # loadable parameters (radix_attention.py:76-80)
-        self.quant_method = None
-        if quant_config is not None:
-            self.quant_method = quant_config.get_quant_method(self, prefix=prefix)
-        if self.quant_method is not None:
-            self.quant_method.create_weights(self)
+        method = quant_config.get_quant_method(self, prefix=prefix) if quant_config is not None else None
+        self.quant_method = method
+        if method is not None:
+            method.create_weights(self)
 
     def forward(self, q, k, v, forward_batch, save_kv_cache: bool = True, **kwargs):
         if k is not None:
