@@ -12,6 +12,12 @@
  * Each function cites the reference interface (file:line under the reference
  * tree) it replaces.  Strides are in ELEMENTS of the tensor's dtype unless the
  * name says bytes.
+ *
+ * Process model: ONE GPU PER PROCESS (the reference's own model: one scheduler / model-runner
+ * process per TP rank, managers/scheduler.py run_scheduler_process).  Kernel attributes, the SM
+ * count and the communicator state are cached once per process for the first device used; driving
+ * a second device from the same process is not supported.  b200_attn_decode_noalloc alone keeps
+ * its state per device.
  */
 #ifndef B200_HOTPATH_H_
 #define B200_HOTPATH_H_
