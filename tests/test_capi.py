@@ -56,6 +56,23 @@ def test_host_side_helpers_need_no_gpu(lib_path):
     assert lib.b200_attn_decode_split_align(128, 4) == 48  # 3 warps x 16-token tiles
 
 
+def test_noalloc_decode_rejects_oversize_requests_before_touching_the_gpu(lib_path):
+    """b200_attn_decode_noalloc: the size check against the built-in 8 MiB scratch comes before any
+    CUDA call, so it can be exercised here (pointers are never dereferenced)."""
+    from sglang_security_b200 import _lib
+
+    lib = _lib.load()
+    assert lib.b200_attn_decode_workspace_bytes(64, 32, 128, 8) > (8 << 20)
+    fake = 0x1000
+    rc = lib.b200_attn_decode_noalloc(fake, 4096, fake, fake, 1024, fake, 4096, fake, 64, fake, fake,
+                                      64, 32, 8, 128, 128, 0.088, 0.0, _lib.BF16, 8, None)
+    assert rc == 1
+    msg = lib.b200_last_error().decode()
+    assert "8388608" in msg and "scratch" in msg
+    assert lib.b200_attn_decode_noalloc(fake, 4096, fake, fake, 1024, fake, 4096, fake, 64, fake, fake,
+                                        0, 32, 8, 128, 128, 0.088, 0.0, _lib.BF16, 8, None) == 0  # empty batch
+
+
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     from sglang_security_b200 import _lib
 
