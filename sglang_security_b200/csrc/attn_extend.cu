@@ -20,6 +20,7 @@
 //               (M128 N=D K16 x 4, V consumed as an MN-major B operand); owns the TMEM allocation.
 //   warps 5-7 : gather loaders (cp.async double buffer, slot ids from req_to_token).
 // Two CTAs are co-resident per SM so one CTA's softmax overlaps the other's MMAs.
+#include <cstdlib>
 #include <type_traits>
 
 #include "tc_common.cuh"
@@ -77,7 +78,21 @@ __device__ __forceinline__ uint32_t swz_off(int row, int col) {
   return panel * (ROWS * 128) + row * 128 + ((c ^ (row & 7)) << 4);
 }
 
-template <typename T, int D>
+// three-input max (PTX ISA 8.6, sm_100+): one FMNMX3 per two new elements
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;\n" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+// FAST (round 2): the softmax warps are the limiter (ncu: issue 56 %, ALU 43 %, tensor 36 %), so the
+// per-element instruction count of the common tile is cut from ~7.5 to ~3: the causal / length mask
+// is applied only on tiles that cross the row's last visible key, the row max is taken on the RAW
+// scores with three-input max (scale > 0 commutes with max), scale and max-subtraction are ONE
+// packed FFMA2 per two elements (exp2(s * scale - m)), and the row sum accumulates with FFMA2.
+// Same values up to fp32 rounding of the fused multiply-add.  Not used with logit capping or a
+// non-positive scale (dispatch falls back to the FAST = false instance, unchanged from round 1).
+template <typename T, int D, bool FAST = false>
 __global__ void __launch_bounds__(kExtThreads, 2)
 attn_extend_kernel(const ExtendParams p) {
   using C = ExtendCfg<D>;
@@ -272,14 +287,36 @@ attn_extend_kernel(const ExtendParams p) {
       tc::tc_fence_before();
       tc::mbar_arrive(bar_s_free);
       float mt = -INFINITY;
+      if constexpr (FAST) {
+        const int k0 = j * kKvTile;
+        if (k0 + kKvTile - 1 > limit) {  // the tile crosses this row's last visible key
 #pragma unroll
-      for (int h = 0; h < 2; ++h)
+          for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const float sc = score(v[h][c], j * kKvTile + h * 32 + c);
-          v[h][c] = __float_as_uint(sc);
-          mt = fmaxf(mt, sc);
+            for (int c = 0; c < 32; ++c)
+              if (k0 + h * 32 + c > limit) v[h][c] = 0xff800000u;  // -inf
         }
+        float a0 = -INFINITY, a1 = -INFINITY, a2 = -INFINITY, a3 = -INFINITY;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int c = 0; c < 32; c += 8) {
+            a0 = fmax3(a0, __uint_as_float(v[h][c]), __uint_as_float(v[h][c + 1]));
+            a1 = fmax3(a1, __uint_as_float(v[h][c + 2]), __uint_as_float(v[h][c + 3]));
+            a2 = fmax3(a2, __uint_as_float(v[h][c + 4]), __uint_as_float(v[h][c + 5]));
+            a3 = fmax3(a3, __uint_as_float(v[h][c + 6]), __uint_as_float(v[h][c + 7]));
+          }
+        mt = fmaxf(fmaxf(a0, a1), fmaxf(a2, a3)) * p.qk_scale;  // qk_scale > 0: -inf stays -inf
+      } else {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const float sc = score(v[h][c], j * kKvTile + h * 32 + c);
+            v[h][c] = __float_as_uint(sc);
+            mt = fmaxf(mt, sc);
+          }
+      }
       const float m_new = fmaxf(m, mt);
       const bool need = m_new > m + kRescaleThreshold;  // also true for the first finite max
       bool pv_waited = false;
@@ -306,13 +343,25 @@ attn_extend_kernel(const ExtendParams p) {
       const float m_use = (m == -INFINITY) ? 0.f : m;
       // ---- P = exp2(S - m), 16-bit, packed in registers first
       uint32_t packed[2][16];
+      const float2 sc2 = make_float2(p.qk_scale, p.qk_scale), nm2 = make_float2(-m_use, -m_use);
+      const float2 one2 = make_float2(1.f, 1.f);
+      float2 lsum = make_float2(0.f, 0.f);
 #pragma unroll
       for (int h = 0; h < 2; ++h)
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
-          const float p0 = fast_exp2(__uint_as_float(v[h][2 * c]) - m_use);
-          const float p1 = fast_exp2(__uint_as_float(v[h][2 * c + 1]) - m_use);
-          l += p0 + p1;
+          float p0, p1;
+          if constexpr (FAST) {
+            const float2 x = ffma2(make_float2(__uint_as_float(v[h][2 * c]),
+                                               __uint_as_float(v[h][2 * c + 1])), sc2, nm2);
+            p0 = fast_exp2(x.x);
+            p1 = fast_exp2(x.y);
+            lsum = ffma2(make_float2(p0, p1), one2, lsum);
+          } else {
+            p0 = fast_exp2(__uint_as_float(v[h][2 * c]) - m_use);
+            p1 = fast_exp2(__uint_as_float(v[h][2 * c + 1]) - m_use);
+            l += p0 + p1;
+          }
           if (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
             __nv_bfloat162 t2 = __floats2bfloat162_rn(p0, p1);
             packed[h][c] = *reinterpret_cast<uint32_t*>(&t2);
@@ -321,6 +370,7 @@ attn_extend_kernel(const ExtendParams p) {
             packed[h][c] = *reinterpret_cast<uint32_t*>(&t2);
           }
         }
+      if constexpr (FAST) l += lsum.x + lsum.y;
       if (j > 0 && !pv_waited) {
         tc::mbar_wait(bar_pv_full, (j - 1) & 1u);  // PV(j-1) has finished reading P(j-1)
         tc::tc_fence_after();
@@ -378,10 +428,16 @@ attn_extend_kernel(const ExtendParams p) {
   if (warp == 4) tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
 }
 
-template <typename T, int D>
-static int launch_extend(const ExtendParams& p, int bs, int max_extend_len, cudaStream_t st) {
+// B200_EXTEND_FAST_SOFTMAX=0 selects the round-1 softmax for every call (read per launch: A/B tools flip it)
+static bool extend_fast_softmax_enabled() {
+  const char* e = std::getenv("B200_EXTEND_FAST_SOFTMAX");
+  return !(e && e[0] == '0');
+}
+
+template <typename T, int D, bool FAST>
+static int launch_extend_inst(const ExtendParams& p, int bs, int max_extend_len, cudaStream_t st) {
   using C = ExtendCfg<D>;
-  auto kern = attn_extend_kernel<T, D>;
+  auto kern = attn_extend_kernel<T, D, FAST>;
   static bool attr_done = false;
   if (!attr_done) {
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -396,6 +452,14 @@ static int launch_extend(const ExtendParams& p, int bs, int max_extend_len, cuda
   }
   B200_CHECK_LAUNCH("attn_extend_kernel");
   return 0;
+}
+
+template <typename T, int D>
+static int launch_extend(const ExtendParams& p, int bs, int max_extend_len, cudaStream_t st) {
+  const bool fast = p.logit_cap <= 0.f && p.qk_scale > 0.f && extend_fast_softmax_enabled();
+  note_variant("attn_extend d=%d fast_softmax=%d", D, fast ? 1 : 0);
+  return fast ? launch_extend_inst<T, D, true>(p, bs, max_extend_len, st)
+              : launch_extend_inst<T, D, false>(p, bs, max_extend_len, st);
 }
 
 }  // namespace b200

@@ -22,6 +22,8 @@ def main():
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bench_extend.json"))
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--ab", action="store_true", help="also time the round-1 softmax instance")
+    ap.add_argument("--headline", action="store_true", help="Llama-3.1-8B heads only (6 points)")
     args = ap.parse_args()
     from sglang_security_b200 import _lib
     from sglang_security_b200.layers.attention.b200_backend import B200AttnBackend
@@ -38,6 +40,8 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     rows = []
     shapes = [("llama8b_tp1", 32, 8, 128), ("llama70b_tp8_rank", 8, 1, 128)]
+    if args.headline:
+        shapes = shapes[:1]
     ctxs = [(8, 2048), (4, 8192)] if not args.quick else [(4, 2048)]
     for name, hq, hkv, d in shapes:
         for bs, ctx in ctxs:
@@ -73,18 +77,25 @@ def main():
                     extend_num_tokens=t, req_to_token_pool=rtp, token_to_kv_pool=kvp,
                     attn_backend=backend)
                 backend.init_forward_metadata(fb)
-                for _ in range(2):
-                    layer(q, k, v, fb)
-                torch.cuda.synchronize()
-                _lib.timing_enable(True)
-                for _ in range(args.iters):
-                    flush.zero_()
-                    layer(q, k, v, fb)
-                torch.cuda.synchronize()
-                _lib.timing_enable(False)
-                n, ms = _lib.timing_read("attn_extend")
-                _lib.timing_read("")
-                us = ms / max(n, 1) * 1e3
+
+                def timed(fast):
+                    # the library reads B200_EXTEND_FAST_SOFTMAX per launch (0 = round-1 softmax)
+                    os.environ["B200_EXTEND_FAST_SOFTMAX"] = "1" if fast else "0"
+                    for _ in range(2):
+                        layer(q, k, v, fb)
+                    torch.cuda.synchronize()
+                    _lib.timing_enable(True)
+                    for _ in range(args.iters):
+                        flush.zero_()
+                        layer(q, k, v, fb)
+                    torch.cuda.synchronize()
+                    _lib.timing_enable(False)
+                    n, ms = _lib.timing_read("attn_extend")
+                    _lib.timing_read("")
+                    return ms / max(n, 1) * 1e3
+
+                us_r1 = timed(False) if args.ab else None
+                us = timed(True)
                 flops = 4.0 * hq * d * bs * ext * (prefix + (ext + 1) / 2)
                 tf = flops / (us * 1e-6) / 1e12
                 row = {"shape": name, "Hq": hq, "Hkv": hkv, "D": d, "bs": bs, "ctx": ctx,
@@ -92,6 +103,9 @@ def main():
                        "us_per_launch": round(us, 1), "tflops": round(tf, 1),
                        "frac_of_measured_bf16_peak": round(tf / peak, 3),
                        "prefill_tokens_per_s_per_layer": round(t / (us * 1e-6))}
+                if us_r1 is not None:
+                    row["us_round1_softmax"] = round(us_r1, 1)
+                    row["tflops_round1_softmax"] = round(flops / (us_r1 * 1e-6) / 1e12, 1)
                 print(json.dumps(row), flush=True)
                 rows.append(row)
                 del kvp, rtp, backend
