@@ -228,8 +228,20 @@ def main():
             c = run_case(P, classes, name, kind, args, quant, dtype, tp)
             out.append(c)
             print(name, "tp", tp, {k: tuple(v.shape) for k, v in c["ranks"][-1]["expected"].items()})
+    # convert_to_channelwise (quantization/utils.py:68-88): what Fp8LinearMethod.process_weights_after_loading
+    # does with the per-shard scales of an fp8-serialized checkpoint on the per-channel kernel path (fp8.py:364-370)
+    uns = {"List": List, "Tuple": Tuple, "torch": torch}
+    upath = f"{REF}/quantization/utils.py"
+    fn = [n for n in ast.parse(open(upath).read()).body
+          if isinstance(n, ast.FunctionDef) and n.name == "convert_to_channelwise"]
+    exec(compile(ast.Module(fn, []), upath, "exec"), uns)
+    channelwise = []
+    for scales, widths in [([0.5, 0.25, 2.0], [32, 8, 8]), ([0.125, 3.0], [48, 48]), ([1.5], [64]), (0.75, [16, 4, 4])]:
+        t = torch.tensor(scales, dtype=torch.float32)
+        channelwise.append({"weight_scale": t, "logical_widths": widths,
+                            "expected": uns["convert_to_channelwise"](t.clone(), widths)})
     path = os.path.join(ROOT, "tests", "golden", "weight_loaders.pt")
-    torch.save({"cases": out, "source": "reference parameter.py + linear.py weight_loader_v2, torch " + torch.__version__}, path)
+    torch.save({"cases": out, "channelwise": channelwise, "source": "reference parameter.py + linear.py weight_loader_v2, torch " + torch.__version__}, path)
     print(path, os.path.getsize(path))
 
 

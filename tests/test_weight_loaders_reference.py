@@ -15,8 +15,9 @@ from sglang_security_b200.layers.quantization.awq import AWQConfig
 from sglang_security_b200.layers.quantization.fp8 import Fp8Config
 from sglang_security_b200.layers.quantization.gptq import GPTQConfig
 
-GOLD = torch.load(os.path.join(os.path.dirname(__file__), "golden", "weight_loaders.pt"),
-                  weights_only=False)["cases"]
+_FIXTURE = torch.load(os.path.join(os.path.dirname(__file__), "golden", "weight_loaders.pt"),
+                      weights_only=False)
+GOLD = _FIXTURE["cases"]
 
 
 def _quant_config(quant):
@@ -87,3 +88,26 @@ def test_fixture_covers_the_loader_matrix():
             "qkv_fp8_tensor", "qkv_fp8_block", "row_plain", "row_awq", "row_gptq", "row_fp8_tensor",
             "column_plain"} <= names
     assert any(c["name"] == "qkv_plain" and c["tp"] == 8 for c in GOLD)      # kv heads replicated 4x
+
+
+def test_fp8_per_shard_scales_to_channelwise_equal_reference():
+    """Fp8LinearMethod.process_weights_after_loading on an fp8-serialized per-tensor checkpoint: the
+    per-shard scales become one scale per output channel exactly as the reference's
+    convert_to_channelwise does (quantization/utils.py:68-88), the static input scale becomes its max."""
+    from sglang_security_b200.layers.quantization.fp8_utils import convert_to_channelwise
+
+    assert len(_FIXTURE["channelwise"]) == 4
+    for c in _FIXTURE["channelwise"]:
+        got = convert_to_channelwise(c["weight_scale"], c["logical_widths"])
+        assert got.dtype == c["expected"].dtype and torch.equal(got, c["expected"])
+    # through the layer: QKV at tp 2 (heads 8 / kv 2 / d 4 -> widths 16, 4, 4)
+    cfg = Fp8Config(is_checkpoint_fp8_serialized=True, activation_scheme="static")
+    layer = QKVParallelLinear(32, 4, 8, 2, bias=False, params_dtype=torch.bfloat16, quant_config=cfg,
+                              tp_rank=0, tp_size=2)
+    for sid, val in (("q", 0.5), ("k", 0.25), ("v", 2.0)):
+        layer.weight_scale.weight_loader(layer.weight_scale, torch.tensor(val), sid)
+        layer.input_scale.weight_loader(layer.input_scale, torch.tensor(val * 3), sid)
+    layer.quant_method.process_weights_after_loading(layer)
+    want = torch.tensor([0.5] * 16 + [0.25] * 4 + [2.0] * 4).reshape(24, 1)
+    assert torch.equal(layer.weight_scale.data, want)
+    assert float(layer.input_scale) == 6.0 and tuple(layer.weight.shape) == (32, 24)
